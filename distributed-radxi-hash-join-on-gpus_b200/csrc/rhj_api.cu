@@ -1,0 +1,921 @@
+// rhj_api.cu -- the extern "C" boundary declared in include/rhj.h: context, device
+// memory pool (memory/Pool.cpp), receive windows (data/Window.cpp) and the launch
+// sequences of the four tasks.  Host code here only sizes buffers and launches
+// kernels; every per-tuple operation lives in rhj_kernels.cuh.
+#include "../../include/rhj.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rhj_kernels.cuh"
+
+using namespace rhj;
+
+// -----------------------------------------------------------------------------------
+// errors
+// -----------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+static unsigned long long g_kernel_launches = 0;  // kernels of this library launched by this process
+
+static int fail(int code, const char *fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+
+#define RHJ_CUDA(expr)                                                                         \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess)                                                                     \
+      return fail(RHJ_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define RHJ_CHECK_LAUNCH(name)                                                                  \
+  do {                                                                                         \
+    cudaError_t _e = cudaGetLastError();                                                       \
+    if (_e != cudaSuccess)                                                                     \
+      return fail(RHJ_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(_e));      \
+    ++g_kernel_launches;                                                                       \
+  } while (0)
+
+extern "C" const char *rhj_last_error(void) { return g_last_error.c_str(); }
+extern "C" uint64_t rhj_launch_count(void) { return g_kernel_launches; }
+extern "C" const char *rhj_version(void) { return "rhj_b200 0.1 (sm_100a)"; }
+
+// -----------------------------------------------------------------------------------
+// context
+// -----------------------------------------------------------------------------------
+static constexpr int kMaxRanks = 64;
+static constexpr uint32_t kDefaultChunk = 1u << 16;
+static constexpr uint32_t kDefaultBuildCap = 4096;
+static constexpr uint64_t kAlign = 256;
+
+enum Ev { EV_START, EV_HIST, EV_NET, EV_LOCAL, EV_BP, EV_H2D0, EV_COUNT };
+
+struct rhj_ctx {
+  int rank = 0, nranks = 1, device = 0, sm_count = 148;
+  rhj_config cfg{};
+  uint32_t P = 0, L = 1, key_shift = 0, shift_bits = 0, nowned = 0, NS = 0;
+  uint32_t chunk1 = 0, chunk2 = 0, cap_r = 0, sslice = 0;
+
+  // pool (memory/Pool.cpp)
+  char *pool = nullptr;
+  uint64_t pool_bytes = 0, pool_used = 0;
+
+  // plan
+  bool planned = false;
+  uint64_t max_local[2] = {0, 0}, window_cap[2] = {0, 0};
+  uint32_t max_chunks1[2] = {0, 0}, max_chunks2[2] = {0, 0};
+  uint64_t *window[2] = {nullptr, nullptr};
+  uint64_t *localout[2] = {nullptr, nullptr};
+  void *staged_input[2] = {nullptr, nullptr};
+  uint32_t *chunk1_hist[2] = {nullptr, nullptr};
+  uint32_t *chunk2_hist[2] = {nullptr, nullptr};
+  uint64_t *d_local_hist = nullptr, *d_global = nullptr, *d_base = nullptr, *d_rel = nullptr, *d_abs = nullptr,
+           *d_dest = nullptr, *d_winsizes = nullptr;
+  uint32_t *d_assign = nullptr;
+  uint64_t *d_part_off = nullptr, *d_part_cnt = nullptr;
+  uint32_t *d_cstart = nullptr;
+  uint64_t *d_sub_tot = nullptr, *d_sub_off = nullptr, *d_sub_prefix = nullptr, *d_sub_addr = nullptr;
+  uint32_t *d_sub_cnt = nullptr;
+  uint64_t *d_item_lstart = nullptr, *d_item_jcount = nullptr, *d_item_jstart = nullptr;
+  unsigned long long *d_work = nullptr, *d_result = nullptr;
+  int *d_status = nullptr;
+
+  // peers (data/Window.cpp: target of MPI_Put)
+  uint64_t peer_window[2][kMaxRanks] = {};
+  void *ipc_base[kMaxRanks] = {};
+
+  // per-join state
+  const void *input[2] = {nullptr, nullptr};
+  uint64_t input_n[2] = {0, 0};
+  uint32_t nchunks1[2] = {0, 0};
+  int stage = 0;  // 0 idle, 1 histogram done, 2 offsets, 3 network, 4 local, 5 build-probe
+  bool local_planned = false;
+  cudaEvent_t ev[EV_COUNT] = {};
+  bool ev_valid[EV_COUNT] = {};
+  double h2d_us = 0;
+};
+
+static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+static int validate_config(const rhj_config *c, int rank, int nranks) {
+  if (!c) return fail(RHJ_ERR_INVALID, "config is NULL");
+  if (nranks < 1 || nranks > kMaxRanks) return fail(RHJ_ERR_INVALID, "nranks %d outside [1,%d]", nranks, kMaxRanks);
+  if (rank < 0 || rank >= nranks) return fail(RHJ_ERR_INVALID, "rank %d outside [0,%d)", rank, nranks);
+  if (c->network_fanout_bits < 1 || c->network_fanout_bits > 12)
+    return fail(RHJ_ERR_INVALID, "network_fanout_bits %u outside [1,12]", c->network_fanout_bits);
+  if (c->local_fanout_bits < 1 || c->local_fanout_bits > 12)
+    return fail(RHJ_ERR_INVALID, "local_fanout_bits %u outside [1,12]", c->local_fanout_bits);
+  uint32_t ks = c->network_fanout_bits + c->payload_bits;
+  if (ks < 1 || ks + c->local_fanout_bits > 63)
+    return fail(RHJ_ERR_INVALID, "network_fanout_bits + payload_bits + local_fanout_bits = %u must be in [2,63]",
+                ks + c->local_fanout_bits);
+  if (c->tuple_bytes != 16 && c->tuple_bytes != 8) return fail(RHJ_ERR_INVALID, "tuple_bytes must be 16 or 8");
+  if (c->allocation_factor != 0 && c->allocation_factor < 1.0)
+    return fail(RHJ_ERR_INVALID, "allocation_factor must be >= 1.0");
+  uint32_t cap = c->build_capacity ? c->build_capacity : kDefaultBuildCap;
+  if (cap != 1024 && cap != 2048 && cap != 4096 && cap != 8192)
+    return fail(RHJ_ERR_INVALID, "build_capacity must be 1024, 2048, 4096 or 8192");
+  uint32_t chunk = c->chunk_tuples ? c->chunk_tuples : kDefaultChunk;
+  if (chunk % kScatTile != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kScatTile);
+  return RHJ_OK;
+}
+
+static uint32_t owned_partitions(uint32_t P, int rank, int nranks) {
+  return (uint32_t)rank < P ? (P - rank + nranks - 1) / nranks : 0;
+}
+
+extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const rhj_config *cfg) {
+  if (!out) return fail(RHJ_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  int rc = validate_config(cfg, rank, nranks);
+  if (rc) return rc;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(RHJ_ERR_CUDA, "no CUDA device available (%s); this library has no CPU path",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  if (device < 0 || device >= ndev) return fail(RHJ_ERR_INVALID, "device %d outside [0,%d)", device, ndev);
+  RHJ_CUDA(cudaSetDevice(device));
+  rhj_ctx *c = new rhj_ctx();
+  c->rank = rank;
+  c->nranks = nranks;
+  c->device = device;
+  c->cfg = *cfg;
+  if (c->cfg.allocation_factor == 0) c->cfg.allocation_factor = 1.1;  // core/Configuration.h:35
+  c->P = 1u << cfg->network_fanout_bits;
+  c->L = cfg->enable_two_level ? (1u << cfg->local_fanout_bits) : 1u;
+  c->key_shift = cfg->network_fanout_bits + cfg->payload_bits;
+  c->shift_bits = c->key_shift + cfg->local_fanout_bits;  // tasks/BuildProbe.cpp:55-57
+  c->nowned = owned_partitions(c->P, rank, nranks);
+  c->NS = c->nowned * c->L;
+  c->chunk1 = c->chunk2 = cfg->chunk_tuples ? cfg->chunk_tuples : kDefaultChunk;
+  c->cap_r = cfg->build_capacity ? cfg->build_capacity : kDefaultBuildCap;
+  c->sslice = 4 * c->cap_r;
+  cudaDeviceProp prop;
+  RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
+  *out = c;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_pool_free_all(rhj_ctx *ctx) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  cudaSetDevice(ctx->device);
+  if (ctx->pool) cudaFree(ctx->pool);
+  ctx->pool = nullptr;
+  ctx->pool_bytes = ctx->pool_used = 0;
+  ctx->planned = false;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_destroy(rhj_ctx *ctx) {
+  if (!ctx) return RHJ_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < kMaxRanks; ++r)
+    if (ctx->ipc_base[r]) cudaIpcCloseMemHandle(ctx->ipc_base[r]);
+  rhj_pool_free_all(ctx);
+  for (int i = 0; i < EV_COUNT; ++i)
+    if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  delete ctx;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_pool_allocate(rhj_ctx *ctx, uint64_t bytes) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->pool) return fail(RHJ_ERR_STATE, "pool already allocated (%llu bytes)", (unsigned long long)ctx->pool_bytes);
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  bytes = align_up(bytes ? bytes : kAlign, kAlign);
+  void *p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess)
+    return fail(RHJ_ERR_NOMEM, "cudaMalloc of %llu pool bytes failed: %s", (unsigned long long)bytes, cudaGetErrorString(e));
+  ctx->pool = static_cast<char *>(p);
+  ctx->pool_bytes = bytes;
+  ctx->pool_used = 0;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_pool_get_memory(rhj_ctx *ctx, uint64_t bytes, void **out_dev) {
+  if (!ctx || !out_dev) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (!ctx->pool) return fail(RHJ_ERR_STATE, "pool not allocated");
+  uint64_t need = align_up(bytes ? bytes : 1, kAlign);
+  if (ctx->pool_used + need > ctx->pool_bytes)
+    return fail(RHJ_ERR_NOMEM, "pool exhausted: %llu used + %llu requested > %llu", (unsigned long long)ctx->pool_used,
+                (unsigned long long)need, (unsigned long long)ctx->pool_bytes);
+  *out_dev = ctx->pool + ctx->pool_used;
+  ctx->pool_used += need;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_pool_reset(rhj_ctx *ctx) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  ctx->pool_used = 0;
+  ctx->planned = false;
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// plan: sizes of every intermediate
+// -----------------------------------------------------------------------------------
+struct Layout {
+  uint64_t window_cap[2], localout_tuples[2];
+  uint32_t max_chunks1[2], max_chunks2[2];
+  uint64_t total;
+};
+
+static uint64_t default_window_cap(const rhj_config *cfg, uint64_t max_local) {
+  double f = cfg->allocation_factor == 0 ? 1.1 : cfg->allocation_factor;
+  return (uint64_t)((double)max_local * f) + 1024;
+}
+
+static void compute_layout(const rhj_config *cfg, int rank, int nranks, const uint64_t max_local[2],
+                           const uint64_t wcap_in[2], Layout *lay) {
+  const uint32_t P = 1u << cfg->network_fanout_bits;
+  const uint32_t L = cfg->enable_two_level ? (1u << cfg->local_fanout_bits) : 1u;
+  const uint32_t nowned = owned_partitions(P, rank, nranks);
+  const uint64_t NS = (uint64_t)nowned * L;
+  const uint32_t chunk = cfg->chunk_tuples ? cfg->chunk_tuples : kDefaultChunk;
+  uint64_t total = 0;
+  auto add = [&](uint64_t bytes) { total += align_up(bytes ? bytes : 1, kAlign); };
+  for (int k = 0; k < 2; ++k) {
+    lay->window_cap[k] = wcap_in[k] ? wcap_in[k] : default_window_cap(cfg, max_local[k]);
+    lay->localout_tuples[k] = cfg->enable_two_level ? lay->window_cap[k] + NS * 8 : 0;
+    lay->max_chunks1[k] = (uint32_t)std::max<uint64_t>(1, (max_local[k] + chunk - 1) / chunk);
+    lay->max_chunks2[k] = cfg->enable_two_level ? (uint32_t)((lay->window_cap[k] + chunk - 1) / chunk + nowned) : 0;
+    add(lay->window_cap[k] * 8);
+    if (cfg->enable_two_level) add(lay->localout_tuples[k] * 8);
+    if (cfg->flags & RHJ_FLAG_STAGE_HOST_INPUTS) add(max_local[k] * cfg->tuple_bytes);
+    add((uint64_t)lay->max_chunks1[k] * P * 4);
+    if (cfg->enable_two_level) add((uint64_t)lay->max_chunks2[k] * L * 4);
+  }
+  for (int i = 0; i < 6; ++i) add(2ull * P * 8);   // local, global, base, rel, abs, dest
+  add((uint64_t)P * 4);                            // assignment
+  add(2ull * nranks * 8);                          // window sizes
+  add(2ull * nowned * 8); add(2ull * nowned * 8);  // part_off, part_cnt
+  add(2ull * (nowned + 1) * 4);                    // cstart
+  for (int i = 0; i < 4; ++i) add(2 * NS * 8);     // sub_tot, sub_off, sub_prefix, sub_addr
+  add(2 * NS * 4);                                 // sub_cnt
+  add(NS * 8); add((uint64_t)nowned * 8); add(((uint64_t)nowned + 1) * 8);  // item_lstart, jcount, jstart
+  add(8); add(5 * 8); add(4);                      // work counter, result, status
+  lay->total = total;
+}
+
+extern "C" uint64_t rhj_workspace_bytes(const rhj_config *cfg, int nranks, uint64_t max_local_inner,
+                                        uint64_t max_local_outer, uint64_t window_inner_cap, uint64_t window_outer_cap) {
+  if (!cfg || validate_config(cfg, 0, nranks)) return 0;
+  Layout lay;
+  uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
+  compute_layout(cfg, 0, nranks, ml, wc, &lay);  // rank 0 owns the most partitions
+  return lay.total;
+}
+
+template <typename T>
+static int carve(rhj_ctx *ctx, uint64_t count, T **out) {
+  void *p = nullptr;
+  int rc = rhj_pool_get_memory(ctx, count * sizeof(T), &p);
+  *out = static_cast<T *>(p);
+  return rc;
+}
+
+extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_local_outer, uint64_t window_inner_cap,
+                        uint64_t window_outer_cap) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->planned) return fail(RHJ_ERR_STATE, "already planned; rhj_pool_reset first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
+  Layout lay;
+  compute_layout(&ctx->cfg, ctx->rank, ctx->nranks, ml, wc, &lay);
+  for (int k = 0; k < 2; ++k) {
+    if (ml[k] >= (1ull << 32) || lay.window_cap[k] >= (1ull << 32))
+      return fail(RHJ_ERR_INVALID, "relation %d: per-rank sizes must stay below 2^32 tuples", k);
+  }
+  if (!ctx->pool) {
+    int rc = rhj_pool_allocate(ctx, lay.total);
+    if (rc) return rc;
+  }
+  if (ctx->pool_bytes - ctx->pool_used < lay.total)
+    return fail(RHJ_ERR_NOMEM, "pool has %llu free bytes, plan needs %llu", (unsigned long long)(ctx->pool_bytes - ctx->pool_used),
+                (unsigned long long)lay.total);
+  const uint32_t P = ctx->P, L = ctx->L, nowned = ctx->nowned;
+  const uint64_t NS = ctx->NS;
+  int rc = 0;
+  for (int k = 0; k < 2 && !rc; ++k) {
+    ctx->max_local[k] = ml[k];
+    ctx->window_cap[k] = lay.window_cap[k];
+    ctx->max_chunks1[k] = lay.max_chunks1[k];
+    ctx->max_chunks2[k] = lay.max_chunks2[k];
+    rc = carve(ctx, lay.window_cap[k], &ctx->window[k]);
+    if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, lay.localout_tuples[k], &ctx->localout[k]);
+    if (!rc && (ctx->cfg.flags & RHJ_FLAG_STAGE_HOST_INPUTS)) {
+      char *p = nullptr;
+      rc = carve(ctx, ml[k] * ctx->cfg.tuple_bytes, &p);
+      ctx->staged_input[k] = p;
+    }
+    if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * P, &ctx->chunk1_hist[k]);
+    if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * L, &ctx->chunk2_hist[k]);
+  }
+  if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_local_hist);
+  if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_global);
+  if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_base);
+  if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_rel);
+  if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_abs);
+  if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_dest);
+  if (!rc) rc = carve(ctx, (uint64_t)P, &ctx->d_assign);
+  if (!rc) rc = carve(ctx, 2ull * ctx->nranks, &ctx->d_winsizes);
+  if (!rc) rc = carve(ctx, 2ull * nowned, &ctx->d_part_off);
+  if (!rc) rc = carve(ctx, 2ull * nowned, &ctx->d_part_cnt);
+  if (!rc) rc = carve(ctx, 2ull * (nowned + 1), &ctx->d_cstart);
+  if (!rc) rc = carve(ctx, 2 * NS, &ctx->d_sub_tot);
+  if (!rc) rc = carve(ctx, 2 * NS, &ctx->d_sub_off);
+  if (!rc) rc = carve(ctx, 2 * NS, &ctx->d_sub_prefix);
+  if (!rc) rc = carve(ctx, 2 * NS, &ctx->d_sub_addr);
+  if (!rc) rc = carve(ctx, 2 * NS, &ctx->d_sub_cnt);
+  if (!rc) rc = carve(ctx, NS, &ctx->d_item_lstart);
+  if (!rc) rc = carve(ctx, (uint64_t)nowned, &ctx->d_item_jcount);
+  if (!rc) rc = carve(ctx, (uint64_t)nowned + 1, &ctx->d_item_jstart);
+  if (!rc) rc = carve(ctx, 1ull, &ctx->d_work);
+  if (!rc) rc = carve(ctx, 5ull, &ctx->d_result);
+  if (!rc) rc = carve(ctx, 1ull, &ctx->d_status);
+  if (rc) return rc;
+  RHJ_CUDA(cudaMemset(ctx->d_status, 0, sizeof(int)));
+  RHJ_CUDA(cudaMemset(ctx->d_result, 0, 5 * 8));
+  ctx->peer_window[0][ctx->rank] = reinterpret_cast<uint64_t>(ctx->window[0]);
+  ctx->peer_window[1][ctx->rank] = reinterpret_cast<uint64_t>(ctx->window[1]);
+  ctx->planned = true;
+  ctx->stage = 0;
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// windows across ranks
+// -----------------------------------------------------------------------------------
+extern "C" int rhj_window_export(rhj_ctx *ctx, rhj_window_handle *out) {
+  if (!ctx || !out) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (!ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+  cudaIpcMemHandle_t h;
+  RHJ_CUDA(cudaIpcGetMemHandle(&h, ctx->pool));
+  memcpy(out->ipc, &h, 64);
+  out->inner_offset = reinterpret_cast<char *>(ctx->window[0]) - ctx->pool;
+  out->outer_offset = reinterpret_cast<char *>(ctx->window[1]) - ctx->pool;
+  out->capacity_inner = ctx->window_cap[0];
+  out->capacity_outer = ctx->window_cap[1];
+  return RHJ_OK;
+}
+
+extern "C" int rhj_window_import(rhj_ctx *ctx, int peer_rank, const rhj_window_handle *handle) {
+  if (!ctx || !handle) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (peer_rank < 0 || peer_rank >= ctx->nranks || peer_rank == ctx->rank)
+    return fail(RHJ_ERR_INVALID, "peer rank %d invalid", peer_rank);
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  if (handle->capacity_inner != ctx->window_cap[0] || handle->capacity_outer != ctx->window_cap[1])
+    return fail(RHJ_ERR_INVALID, "peer %d planned different window capacities", peer_rank);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle->ipc, 64);
+  void *base = nullptr;
+  RHJ_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+  ctx->ipc_base[peer_rank] = base;
+  ctx->peer_window[0][peer_rank] = reinterpret_cast<uint64_t>(static_cast<char *>(base) + handle->inner_offset);
+  ctx->peer_window[1][peer_rank] = reinterpret_cast<uint64_t>(static_cast<char *>(base) + handle->outer_offset);
+  return RHJ_OK;
+}
+
+extern "C" int rhj_window_set_peer(rhj_ctx *ctx, int peer_rank, void *inner_window_dev, void *outer_window_dev) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (peer_rank < 0 || peer_rank >= ctx->nranks) return fail(RHJ_ERR_INVALID, "peer rank %d invalid", peer_rank);
+  ctx->peer_window[0][peer_rank] = reinterpret_cast<uint64_t>(inner_window_dev);
+  ctx->peer_window[1][peer_rank] = reinterpret_cast<uint64_t>(outer_window_dev);
+  return RHJ_OK;
+}
+
+extern "C" int rhj_window_get(rhj_ctx *ctx, void **inner_window_dev, void **outer_window_dev) {
+  if (!ctx || !ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
+  if (inner_window_dev) *inner_window_dev = ctx->window[0];
+  if (outer_window_dev) *outer_window_dev = ctx->window[1];
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// launches
+// -----------------------------------------------------------------------------------
+static int record(rhj_ctx *ctx, int which, cudaStream_t st) {
+  RHJ_CUDA(cudaEventRecord(ctx->ev[which], st));
+  ctx->ev_valid[which] = true;
+  return RHJ_OK;
+}
+
+template <class Source, class Map>
+static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+                            uint32_t *chunk_hist, cudaStream_t st) {
+  if (grid_chunks == 0) return RHJ_OK;
+  const bool agg = (ctx->cfg.flags & RHJ_FLAG_HIST_WARP_AGGREGATE) != 0;
+  uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, 4096 / nbins));
+  size_t smem = (size_t)nbins * nrep * 4;
+  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 4);
+  if (agg)
+    k_histogram<Source, Map, true><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, chunk_hist, ctx->d_status);
+  else
+    k_histogram<Source, Map, false><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, chunk_hist, ctx->d_status);
+  RHJ_CHECK_LAUNCH("k_histogram");
+  return RHJ_OK;
+}
+
+template <class Source, class Map>
+static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+                          const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+  if (grid_chunks == 0) return RHJ_OK;
+  size_t smem = scatter_smem_bytes(nbins);
+  RHJ_CUDA(cudaFuncSetAttribute(k_scatter<Source, Map>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 2);
+  k_scatter<Source, Map><<<grid, kScatTPB, smem, st>>>(src, cm, nbins, chunk_off, bin_base, ctx->d_status);
+  RHJ_CHECK_LAUNCH("k_scatter");
+  return RHJ_OK;
+}
+
+template <int TB>
+static int histogram_inputs(rhj_ctx *ctx, cudaStream_t st) {
+  for (int k = 0; k < 2; ++k) {
+    InputSource<TB> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+    ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
+    int rc = launch_histogram(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], st);
+    if (rc) return rc;
+    dim3 grid((ctx->P + 31) / 32, 1);
+    k_colscan<32><<<grid, 32 * 32, 0, st>>>(ctx->chunk1_hist[k], ctx->P, nullptr, ctx->nchunks1[k],
+                                             ctx->d_local_hist + (uint64_t)k * ctx->P, ctx->d_status);
+    RHJ_CHECK_LAUNCH("k_colscan");
+  }
+  return RHJ_OK;
+}
+
+extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *outer_dev,
+                             uint64_t outer_n, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (!ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
+  if (inner_n > ctx->max_local[0] || outer_n > ctx->max_local[1])
+    return fail(RHJ_ERR_INVALID, "relation sizes (%llu, %llu) exceed the planned maxima (%llu, %llu)",
+                (unsigned long long)inner_n, (unsigned long long)outer_n, (unsigned long long)ctx->max_local[0],
+                (unsigned long long)ctx->max_local[1]);
+  if ((inner_n && !inner_dev) || (outer_n && !outer_dev)) return fail(RHJ_ERR_INVALID, "NULL relation pointer");
+  if ((reinterpret_cast<uintptr_t>(inner_dev) | reinterpret_cast<uintptr_t>(outer_dev)) & (ctx->cfg.tuple_bytes - 1))
+    return fail(RHJ_ERR_INVALID, "relations must be %u-byte aligned", ctx->cfg.tuple_bytes);
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ctx->input[0] = inner_dev;
+  ctx->input[1] = outer_dev;
+  ctx->input_n[0] = inner_n;
+  ctx->input_n[1] = outer_n;
+  for (int k = 0; k < 2; ++k) ctx->nchunks1[k] = (uint32_t)((ctx->input_n[k] + ctx->chunk1 - 1) / ctx->chunk1);
+  ctx->local_planned = false;
+  int rc = record(ctx, EV_START, st);
+  if (rc) return rc;
+  RHJ_CUDA(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), st));
+  RHJ_CUDA(cudaMemsetAsync(ctx->d_result, 0, 5 * 8, st));
+  rc = ctx->cfg.tuple_bytes == 16 ? histogram_inputs<16>(ctx, st) : histogram_inputs<8>(ctx, st);
+  if (rc) return rc;
+  ctx->stage = 1;
+  return RHJ_OK;
+}
+
+extern "C" uint64_t *rhj_local_histogram_dev(rhj_ctx *ctx) { return ctx ? ctx->d_local_hist : nullptr; }
+
+extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->stage < 1) return fail(RHJ_ERR_STATE, "rhj_histogram first");
+  if (!gathered_dev && ctx->nranks > 1) return fail(RHJ_ERR_INVALID, "gathered histograms required when nranks > 1");
+  for (int r = 0; r < ctx->nranks; ++r)
+    if (!ctx->peer_window[0][r] || !ctx->peer_window[1][r])
+      return fail(RHJ_ERR_STATE, "window of rank %d not imported (rhj_window_import / rhj_window_set_peer)", r);
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PlanNetworkArgs a{};
+  a.gathered = gathered_dev ? gathered_dev : ctx->d_local_hist;
+  a.nranks = ctx->nranks;
+  a.rank = ctx->rank;
+  a.parts = ctx->P;
+  for (int k = 0; k < 2; ++k) {
+    a.window_cap[k] = ctx->window_cap[k];
+    a.max_chunks2[k] = ctx->cfg.enable_two_level ? ctx->max_chunks2[k] : 0xFFFFFFFFu;
+    for (int r = 0; r < ctx->nranks; ++r) a.peer_window[k][r] = ctx->peer_window[k][r];
+  }
+  a.global_hist = ctx->d_global;
+  a.base = ctx->d_base;
+  a.rel = ctx->d_rel;
+  a.abs = ctx->d_abs;
+  a.dest = ctx->d_dest;
+  a.assignment = ctx->d_assign;
+  a.window_sizes = ctx->d_winsizes;
+  a.nowned = ctx->nowned;
+  a.part_off = ctx->d_part_off;
+  a.part_cnt = ctx->d_part_cnt;
+  a.cstart = ctx->d_cstart;
+  a.chunk2 = ctx->chunk2;
+  a.status = ctx->d_status;
+  k_plan_network<<<1, 1024, ((size_t)ctx->P + 1) * 8, st>>>(a);
+  RHJ_CHECK_LAUNCH("k_plan_network");
+  int rc = record(ctx, EV_HIST, st);
+  if (rc) return rc;
+  ctx->stage = 2;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->stage < 2) return fail(RHJ_ERR_STATE, "rhj_compute_offsets first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (int k = 0; k < 2; ++k) {
+    ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
+    int rc;
+    if (ctx->cfg.tuple_bytes == 16) {
+      InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
+    } else {
+      InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
+    }
+    if (rc) return rc;
+  }
+  int rc = record(ctx, EV_NET, st);
+  if (rc) return rc;
+  ctx->stage = 3;
+  return RHJ_OK;
+}
+
+static int launch_plan_local(rhj_ctx *ctx, cudaStream_t st) {
+  if (ctx->nowned == 0) {
+    RHJ_CUDA(cudaMemsetAsync(ctx->d_item_jstart, 0, 8, st));
+    ctx->local_planned = true;
+    return RHJ_OK;
+  }
+  PlanLocalArgs a{};
+  a.nowned = ctx->nowned;
+  a.L = ctx->L;
+  a.two_level = ctx->cfg.enable_two_level ? 1 : 0;
+  a.part_off = ctx->d_part_off;
+  a.part_cnt = ctx->d_part_cnt;
+  a.sub_tot = ctx->d_sub_tot;
+  for (int k = 0; k < 2; ++k) {
+    a.out_base[k] = reinterpret_cast<uint64_t>(ctx->localout[k]);
+    a.win_base[k] = reinterpret_cast<uint64_t>(ctx->window[k]);
+  }
+  a.sub_off = ctx->d_sub_off;
+  a.sub_prefix = ctx->d_sub_prefix;
+  a.sub_addr = ctx->d_sub_addr;
+  a.sub_cnt = ctx->d_sub_cnt;
+  a.item_lstart = ctx->d_item_lstart;
+  a.item_jcount = ctx->d_item_jcount;
+  a.cap_r = ctx->cap_r;
+  a.sslice = ctx->sslice;
+  k_plan_local<<<ctx->nowned, 256, 0, st>>>(a);
+  RHJ_CHECK_LAUNCH("k_plan_local");
+  k_plan_items<<<1, 1024, 0, st>>>(ctx->d_item_jcount, ctx->nowned, ctx->d_item_jstart, ctx->d_work);
+  RHJ_CHECK_LAUNCH("k_plan_items");
+  ctx->local_planned = true;
+  return RHJ_OK;
+}
+
+extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (ctx->cfg.enable_two_level && ctx->nowned > 0) {
+    const uint32_t L = ctx->L;
+    for (int k = 0; k < 2; ++k) {
+      ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
+      ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
+                     ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
+      int rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], st);
+      if (rc) return rc;
+      dim3 grid((L + 31) / 32, ctx->nowned);
+      k_colscan<8><<<grid, 8 * 32, 0, st>>>(ctx->chunk2_hist[k], L, ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), 0,
+                                             ctx->d_sub_tot + (uint64_t)k * ctx->NS, ctx->d_status);
+      RHJ_CHECK_LAUNCH("k_colscan(local)");
+    }
+    int rc = launch_plan_local(ctx, st);
+    if (rc) return rc;
+    for (int k = 0; k < 2; ++k) {
+      ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
+      ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
+                     ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
+      rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k],
+                          ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
+      if (rc) return rc;
+    }
+  }
+  int rc = record(ctx, EV_LOCAL, st);
+  if (rc) return rc;
+  ctx->stage = 4;
+  return RHJ_OK;
+}
+
+template <int CAP>
+static int launch_build_probe(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_t st) {
+  size_t smem = build_probe_smem_bytes<CAP>();
+  RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_build_probe<CAP>, kBpTPB, smem));
+  if (per_sm < 1) per_sm = 1;
+  k_build_probe<CAP><<<ctx->sm_count * per_sm, kBpTPB, smem, st>>>(a);
+  RHJ_CHECK_LAUNCH("k_build_probe");
+  return RHJ_OK;
+}
+
+extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!ctx->local_planned) {
+    int rc = launch_plan_local(ctx, st);
+    if (rc) return rc;
+  }
+  if (ctx->nowned > 0) {
+    BuildProbeArgs a{};
+    for (int k = 0; k < 2; ++k) a.src[k] = ctx->cfg.enable_two_level ? ctx->localout[k] : ctx->window[k];
+    a.sub_off = ctx->d_sub_off;
+    a.sub_cnt = ctx->d_sub_cnt;
+    a.item_lstart = ctx->d_item_lstart;
+    a.item_jstart = ctx->d_item_jstart;
+    a.work_counter = ctx->d_work;
+    a.result = ctx->d_result;
+    a.nowned = ctx->nowned;
+    a.L = ctx->L;
+    a.NS = ctx->NS;
+    a.rank = ctx->rank;
+    a.nranks = ctx->nranks;
+    a.net_bits = ctx->cfg.network_fanout_bits;
+    a.key_shift = ctx->key_shift;
+    a.shift_bits = ctx->shift_bits;
+    a.sslice = ctx->sslice;
+    a.status = ctx->d_status;
+    int rc;
+    switch (ctx->cap_r) {
+      case 1024: rc = launch_build_probe<1024>(ctx, a, st); break;
+      case 2048: rc = launch_build_probe<2048>(ctx, a, st); break;
+      case 8192: rc = launch_build_probe<8192>(ctx, a, st); break;
+      default: rc = launch_build_probe<4096>(ctx, a, st); break;
+    }
+    if (rc) return rc;
+  }
+  int rc = record(ctx, EV_BP, st);
+  if (rc) return rc;
+  ctx->stage = 5;
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// getters
+// -----------------------------------------------------------------------------------
+static int copy_out(rhj_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream) {
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RHJ_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st));
+  RHJ_CUDA(cudaStreamSynchronize(st));
+  return RHJ_OK;
+}
+
+extern "C" int rhj_get_assignment(rhj_ctx *ctx, uint32_t *out_host, void *stream) {
+  if (!ctx || !out_host) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (ctx->stage < 2) return fail(RHJ_ERR_STATE, "rhj_compute_offsets first");
+  return copy_out(ctx, out_host, ctx->d_assign, (size_t)ctx->P * 4, stream);
+}
+
+static int get_u64(rhj_ctx *ctx, int which, const uint64_t *arr, int min_stage, uint64_t *out_host, void *stream) {
+  if (!ctx || !out_host) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (ctx->stage < min_stage) return fail(RHJ_ERR_STATE, "stage not reached");
+  return copy_out(ctx, out_host, arr + (uint64_t)which * ctx->P, (size_t)ctx->P * 8, stream);
+}
+
+extern "C" int rhj_get_local_histogram(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream) {
+  return get_u64(ctx, which, ctx ? ctx->d_local_hist : nullptr, 1, out_host, stream);
+}
+extern "C" int rhj_get_global_histogram(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream) {
+  return get_u64(ctx, which, ctx ? ctx->d_global : nullptr, 2, out_host, stream);
+}
+extern "C" int rhj_get_base_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream) {
+  return get_u64(ctx, which, ctx ? ctx->d_base : nullptr, 2, out_host, stream);
+}
+extern "C" int rhj_get_write_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream) {
+  return get_u64(ctx, which, ctx ? ctx->d_abs : nullptr, 2, out_host, stream);
+}
+
+extern "C" int rhj_get_local_partition(rhj_ctx *ctx, int which, uint32_t p, uint64_t *hist_host, uint64_t *prefix_host,
+                                       void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 or 1");
+  if (!ctx->cfg.enable_two_level) return fail(RHJ_ERR_STATE, "two-level partitioning is off");
+  if (ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
+  if (p >= ctx->P || p % ctx->nranks != (uint32_t)ctx->rank) return fail(RHJ_ERR_INVALID, "partition %u not owned by rank %d", p, ctx->rank);
+  uint32_t j = p / ctx->nranks;
+  std::vector<uint32_t> cnt(ctx->L);
+  int rc = copy_out(ctx, cnt.data(), ctx->d_sub_cnt + (uint64_t)which * ctx->NS + (uint64_t)j * ctx->L, (size_t)ctx->L * 4, stream);
+  if (rc) return rc;
+  if (hist_host)
+    for (uint32_t l = 0; l < ctx->L; ++l) hist_host[l] = cnt[l];
+  if (prefix_host)
+    rc = copy_out(ctx, prefix_host, ctx->d_sub_prefix + (uint64_t)which * ctx->NS + (uint64_t)j * ctx->L, (size_t)ctx->L * 8, stream);
+  return rc;
+}
+
+extern "C" int rhj_get_partition_dev(rhj_ctx *ctx, int which, uint32_t p, int after_local_pass, void **out_dev,
+                                     uint64_t *out_tuples) {
+  if (!ctx || !out_dev || !out_tuples) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 or 1");
+  if (ctx->stage < (after_local_pass ? 4 : 3)) return fail(RHJ_ERR_STATE, "stage not reached");
+  if (after_local_pass && !ctx->cfg.enable_two_level) return fail(RHJ_ERR_STATE, "two-level partitioning is off");
+  if (p >= ctx->P || p % ctx->nranks != (uint32_t)ctx->rank) return fail(RHJ_ERR_INVALID, "partition %u not owned by rank %d", p, ctx->rank);
+  uint32_t j = p / ctx->nranks;
+  uint64_t off = 0, cnt = 0;
+  int rc = copy_out(ctx, &off, ctx->d_part_off + (uint64_t)which * ctx->nowned + j, 8, nullptr);
+  if (!rc) rc = copy_out(ctx, &cnt, ctx->d_part_cnt + (uint64_t)which * ctx->nowned + j, 8, nullptr);
+  if (rc) return rc;
+  if (after_local_pass) {
+    *out_dev = ctx->localout[which] + off + (uint64_t)j * ctx->L * 8;
+    *out_tuples = cnt + (uint64_t)ctx->L * 8;
+  } else {
+    *out_dev = ctx->window[which] + off;
+    *out_tuples = cnt;
+  }
+  return RHJ_OK;
+}
+
+extern "C" int rhj_get_result(rhj_ctx *ctx, rhj_result *out, void *stream) {
+  if (!ctx || !out) return fail(RHJ_ERR_INVALID, "NULL argument");
+  if (ctx->stage < 5) return fail(RHJ_ERR_STATE, "rhj_build_probe first");
+  unsigned long long r[5];
+  int status = 0;
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RHJ_CUDA(cudaMemcpyAsync(r, ctx->d_result, sizeof(r), cudaMemcpyDeviceToHost, st));
+  RHJ_CUDA(cudaMemcpyAsync(&status, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, st));
+  RHJ_CUDA(cudaStreamSynchronize(st));
+  if (status == kDevWindowOverflow)
+    return fail(RHJ_ERR_CAPACITY, "a receive window is smaller than the tuples assigned to it; raise allocation_factor or the window capacity");
+  if (status != kDevOk) return fail(RHJ_ERR_CAPACITY, "device workspace bound exceeded (status %d)", status);
+  out->matches = r[0];
+  out->sum_key = r[1];
+  out->sum_rid_r = r[2];
+  out->sum_rid_s = r[3];
+  out->sum_mix = r[4];
+  return RHJ_OK;
+}
+
+extern "C" int rhj_get_timings(rhj_ctx *ctx, rhj_timings *out) {
+  if (!ctx || !out) return fail(RHJ_ERR_INVALID, "NULL argument");
+  memset(out, 0, sizeof(*out));
+  if (ctx->stage < 5) return fail(RHJ_ERR_STATE, "no finished join");
+  auto us = [&](int a, int b) -> double {
+    float ms = 0;
+    if (!ctx->ev_valid[a] || !ctx->ev_valid[b]) return 0.0;
+    if (cudaEventElapsedTime(&ms, ctx->ev[a], ctx->ev[b]) != cudaSuccess) { cudaGetLastError(); return 0.0; }
+    return (double)ms * 1000.0;
+  };
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  RHJ_CUDA(cudaEventSynchronize(ctx->ev[EV_BP]));
+  out->jtotal_us = us(EV_START, EV_BP);
+  out->jhist_us = us(EV_START, EV_HIST);
+  out->jmpi_us = us(EV_HIST, EV_NET);
+  out->jproc_us = us(EV_NET, EV_BP);
+  out->lp_us = us(EV_NET, EV_LOCAL);
+  out->bp_us = us(EV_LOCAL, EV_BP);
+  out->h2d_us = ctx->h2d_us;
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// the operator (operators/HashJoin.cpp:45-220), single rank
+// -----------------------------------------------------------------------------------
+extern "C" int rhj_join(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *outer_dev, uint64_t outer_n,
+                        void *stream, rhj_result *out) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (ctx->nranks != 1)
+    return fail(RHJ_ERR_STATE, "rhj_join drives a single rank; with %d ranks call the stages and all-gather "
+                "rhj_local_histogram_dev() between rhj_histogram and rhj_compute_offsets", ctx->nranks);
+  if (!ctx->planned) {
+    int rc = rhj_plan(ctx, inner_n, outer_n, 0, 0);
+    if (rc) return rc;
+  }
+  ctx->h2d_us = 0;
+  int rc = rhj_histogram(ctx, inner_dev, inner_n, outer_dev, outer_n, stream);
+  if (!rc) rc = rhj_compute_offsets(ctx, nullptr, stream);
+  if (!rc) rc = rhj_network_partition(ctx, stream);
+  if (!rc) rc = rhj_local_partition(ctx, stream);
+  if (!rc) rc = rhj_build_probe(ctx, stream);
+  if (!rc && out) rc = rhj_get_result(ctx, out, stream);
+  return rc;
+}
+
+extern "C" int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host,
+                             uint64_t outer_n, void *stream, rhj_result *out) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (!(ctx->cfg.flags & RHJ_FLAG_STAGE_HOST_INPUTS))
+    return fail(RHJ_ERR_STATE, "rhj_join_host needs RHJ_FLAG_STAGE_HOST_INPUTS in rhj_config.flags (device staging buffers)");
+  if (!ctx->planned) {
+    int rc = rhj_plan(ctx, inner_n, outer_n, 0, 0);
+    if (rc) return rc;
+  }
+  if (inner_n > ctx->max_local[0] || outer_n > ctx->max_local[1])
+    return fail(RHJ_ERR_INVALID, "relation sizes exceed the planned maxima");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RHJ_CUDA(cudaEventRecord(ctx->ev[EV_H2D0], st));
+  RHJ_CUDA(cudaMemcpyAsync(ctx->staged_input[0], inner_host, inner_n * ctx->cfg.tuple_bytes, cudaMemcpyHostToDevice, st));
+  RHJ_CUDA(cudaMemcpyAsync(ctx->staged_input[1], outer_host, outer_n * ctx->cfg.tuple_bytes, cudaMemcpyHostToDevice, st));
+  int rc = rhj_join(ctx, ctx->staged_input[0], inner_n, ctx->staged_input[1], outer_n, stream, out);
+  if (rc) return rc;
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, ctx->ev[EV_H2D0], ctx->ev[EV_START]) == cudaSuccess) ctx->h2d_us = ms * 1000.0;
+  else cudaGetLastError();
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// device generator
+// -----------------------------------------------------------------------------------
+extern "C" int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n, uint64_t first, uint64_t domain,
+                             uint64_t seed, uint64_t modulo, uint64_t start_key, uint64_t start_rid, void *stream) {
+  if (tuple_bytes != 16 && tuple_bytes != 8) return fail(RHJ_ERR_INVALID, "tuple_bytes must be 16 or 8");
+  if (n == 0) return RHJ_OK;
+  if (!tuples_dev) return fail(RHJ_ERR_INVALID, "NULL tuples");
+  PermParams pp{};
+  pp.domain = domain;
+  uint32_t b = 0;
+  while (b < 64 && (1ull << b) < domain) ++b;
+  pp.mask = b >= 64 ? ~0ull : ((1ull << b) - 1);
+  pp.shift = b / 2 ? b / 2 : 1;
+  pp.m0 = splitmix64(seed) | 1; pp.a0 = splitmix64(seed + 1);
+  pp.m1 = splitmix64(seed + 2) | 1; pp.a1 = splitmix64(seed + 3);
+  pp.m2 = splitmix64(seed + 4) | 1; pp.a2 = splitmix64(seed + 5);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, 148 * 16);
+  if (tuple_bytes == 16) k_fill_perm<16><<<grid, 256, 0, st>>>(tuples_dev, n, first, pp, modulo, start_key, start_rid);
+  else k_fill_perm<8><<<grid, 256, 0, st>>>(tuples_dev, n, first, pp, modulo, start_key, start_rid);
+  RHJ_CHECK_LAUNCH("k_fill_perm");
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// runtime conveniences
+// -----------------------------------------------------------------------------------
+extern "C" int rhj_host_alloc(void **out_host, uint64_t bytes) {
+  if (!out_host) return fail(RHJ_ERR_INVALID, "NULL argument");
+  RHJ_CUDA(cudaHostAlloc(out_host, bytes ? bytes : 1, cudaHostAllocDefault));
+  return RHJ_OK;
+}
+extern "C" int rhj_host_free(void *host) {
+  if (host) RHJ_CUDA(cudaFreeHost(host));
+  return RHJ_OK;
+}
+extern "C" int rhj_memcpy_d2h(void *dst_host, const void *src_dev, uint64_t bytes) {
+  RHJ_CUDA(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+  return RHJ_OK;
+}
+extern "C" int rhj_memcpy_h2d(void *dst_dev, const void *src_host, uint64_t bytes) {
+  RHJ_CUDA(cudaMemcpy(dst_dev, src_host, bytes, cudaMemcpyHostToDevice));
+  return RHJ_OK;
+}
+
+// -----------------------------------------------------------------------------------
+// host-side planning logic (no GPU needed)
+// -----------------------------------------------------------------------------------
+extern "C" void rhj_host_assignment(uint32_t nranks, uint32_t parts, uint32_t *assignment) {
+  for (uint32_t p = 0; p < parts; ++p) assignment[p] = p % nranks;  // histograms/AssignmentMap.cpp:41-43
+}
+
+extern "C" void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32_t rank, uint32_t parts, uint64_t *global,
+                                 uint64_t *base, uint64_t *rel, uint64_t *abs, uint64_t *window_sizes) {
+  std::vector<uint64_t> running(nranks, 0);
+  for (uint32_t p = 0; p < parts; ++p) {
+    uint64_t g = 0, before = 0;
+    for (uint32_t r = 0; r < nranks; ++r) {
+      uint64_t v = locals[(uint64_t)r * parts + p];
+      if (r < rank) before += v;  // histograms/OffsetMap.cpp:78-83 (exclusive scan over ranks)
+      g += v;                     // histograms/GlobalHistogram.cpp:37-42
+    }
+    uint32_t owner = p % nranks;
+    if (global) global[p] = g;
+    if (base) base[p] = running[owner];  // histograms/OffsetMap.cpp:59-73
+    if (rel) rel[p] = before;
+    if (abs) abs[p] = running[owner] + before;  // histograms/OffsetMap.cpp:87-93
+    running[owner] += g;
+  }
+  if (window_sizes)
+    for (uint32_t r = 0; r < nranks; ++r) window_sizes[r] = running[r];  // data/Window.cpp:168-178
+}

@@ -1,0 +1,115 @@
+"""Launcher-side mirror of the reference's operator surface.
+
+`HashJoin(numberOfNodes, nodeId, inner, outer).join()` has the argument meaning of
+hpcjoin::operators::HashJoin (operators/HashJoin.h:23-43); the phases run in the
+order of operators/HashJoin.cpp:45-220, each phase one call through the C ABI.
+With more than one rank (one process per GPU, torch.distributed/NCCL) the only
+communication is: one all-gather of the per-rank histograms (replaces
+MPI_Allreduce + MPI_Exscan), the peer stores issued by the scatter kernel itself
+(replace MPI_Put) and one barrier (operators/HashJoin.cpp:119-121).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+
+class _DeviceArray:
+    """Expose a raw device pointer to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, n: int, typestr: str = "<i8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+class Relation:
+    """Device-resident relation: `local_size` tuples of this rank out of `global_size`
+    (data/Relation.h:18-60).  `data` is a torch tensor (int64) holding Tuple{key,rid}
+    pairs (tuple_bytes 16) or packed 8-byte tuples."""
+
+    def __init__(self, data, local_size: int, global_size: int, tuple_bytes: int = 16):
+        self.data, self.local_size, self.global_size, self.tuple_bytes = data, local_size, global_size, tuple_bytes
+
+    @staticmethod
+    def from_numpy(arr, global_size: int | None = None, device: int = 0) -> "Relation":
+        import numpy as np
+        import torch
+        tb = 16 if arr.dtype.itemsize == 16 else 8
+        flat = np.ascontiguousarray(arr).view(np.int64)
+        t = torch.from_numpy(flat).to(f"cuda:{device}")
+        return Relation(t, len(arr), global_size if global_size is not None else len(arr), tb)
+
+    def getLocalSize(self):
+        return self.local_size
+
+    def getGlobalSize(self):
+        return self.global_size
+
+    def getData(self):
+        return self.data
+
+
+def exchange_windows(ctx, group=None):
+    """Collective: make every rank's receive windows addressable from this rank
+    (replaces MPI_Win_create, data/Window.cpp:35-45) via CUDA IPC."""
+    import torch.distributed as dist
+    from . import WindowHandle
+    if ctx.nranks == 1:
+        return
+    mine = bytes(ctx.window_export())
+    handles = [None] * ctx.nranks
+    dist.all_gather_object(handles, mine, group=group)
+    for r, raw in enumerate(handles):
+        if r != ctx.rank:
+            ctx.window_import(r, WindowHandle.from_buffer_copy(raw))
+
+
+def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None):
+    """operators/HashJoin.cpp:45-220 for this rank; every rank calls it (collective)."""
+    import torch
+    import torch.distributed as dist
+    ctx.histogram(inner.data, inner.local_size, outer.data, outer.local_size)
+    if ctx.nranks > 1:
+        local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr(), 2 * ctx.P), device=f"cuda:{ctx.device}")
+        gathered = torch.empty(ctx.nranks * 2 * ctx.P, dtype=torch.int64, device=local.device)
+        dist.all_gather_into_tensor(gathered, local, group=group)
+        ctx.compute_offsets(gathered)
+    else:
+        ctx.compute_offsets(None)
+    ctx.network_partition()
+    if ctx.nranks > 1:
+        # all peer stores have been issued before any rank reads its window
+        token = torch.zeros(1, dtype=torch.int32, device=f"cuda:{ctx.device}")
+        dist.all_reduce(token, group=group)
+    ctx.local_partition()
+    ctx.build_probe()
+
+
+class HashJoin:
+    """hpcjoin::operators::HashJoin (operators/HashJoin.h:23-43).  RESULT_COUNTER is the
+    class-level match count of the last join on this rank, as in the reference
+    (operators/HashJoin.cpp:28); RESULT_CHECKSUM is this project's addition."""
+
+    RESULT_COUNTER = 0
+    RESULT_CHECKSUM = (0, 0, 0, 0)
+
+    def __init__(self, numberOfNodes: int, nodeId: int, innerRelation: Relation, outerRelation: Relation,
+                 config=None, device: int | None = None, group=None, window_caps=(0, 0)):
+        from . import Context, make_config
+        import torch
+        self.numberOfNodes, self.nodeId = numberOfNodes, nodeId
+        self.innerRelation, self.outerRelation = innerRelation, outerRelation
+        self.group = group
+        cfg = config if config is not None else make_config(tuple_bytes=innerRelation.tuple_bytes)
+        dev = device if device is not None else torch.cuda.current_device()
+        self.ctx = Context(cfg, nodeId, numberOfNodes, dev)
+        self.ctx.plan(innerRelation.local_size, outerRelation.local_size, *window_caps)
+        exchange_windows(self.ctx, group)
+
+    def join(self):
+        join_multi_rank(self.ctx, self.innerRelation, self.outerRelation, self.group)
+        r = self.ctx.result()
+        HashJoin.RESULT_COUNTER = r.matches
+        HashJoin.RESULT_CHECKSUM = (r.sum_key, r.sum_rid_r, r.sum_rid_s, r.sum_mix)
+        return r
+
+    def close(self):
+        self.ctx.close()

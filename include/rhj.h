@@ -1,0 +1,211 @@
+/*
+ * rhj.h -- C ABI of the B200 radix hash join library (librhj_b200.so).
+ *
+ * This is the drop-in boundary for ONE path of
+ * lushl9301/Distributed-Radxi-Hash-Join-on-GPUs: the pipeline behind
+ * hpcjoin::operators::HashJoin::join() (operators/HashJoin.cpp:45-220):
+ * HistogramComputation -> Window -> NetworkPartitioning -> LocalPartitioning ->
+ * BuildProbe.  Citations are file:line in the reference tree.
+ *
+ * Conventions
+ *  - plain C types only; every pointer named *_dev is a device pointer owned by
+ *    the caller unless stated otherwise; `stream` is a cudaStream_t passed as
+ *    void* (NULL = the legacy default stream).
+ *  - every function returns 0 on success or a negative rhj_status; the text of
+ *    the last failure on the calling thread is rhj_last_error().  Nothing in
+ *    the library calls exit() (the reference's JOIN_ASSERT does, utils/Debug.h:27-37).
+ *  - one rhj_ctx per GPU per rank; a context is not thread-safe.
+ *  - no CPU fallback exists: without a CUDA device every compute entry point
+ *    fails with RHJ_ERR_CUDA.
+ */
+#ifndef RHJ_H_
+#define RHJ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rhj_ctx rhj_ctx;
+
+typedef enum rhj_status {
+  RHJ_OK = 0,
+  RHJ_ERR_INVALID = -1,   /* bad argument / configuration */
+  RHJ_ERR_CUDA = -2,      /* CUDA runtime failure (message has the CUDA text) */
+  RHJ_ERR_NOMEM = -3,     /* pool exhausted */
+  RHJ_ERR_CAPACITY = -4,  /* a receive window / workspace bound was exceeded on the device */
+  RHJ_ERR_STATE = -5      /* stage called out of order */
+} rhj_status;
+
+/* Replaces the compile-time knobs of core/Configuration.h:19-38. */
+typedef struct rhj_config {
+  uint32_t network_fanout_bits; /* NETWORK_PARTITIONING_FANOUT (:30), 1..12 */
+  uint32_t local_fanout_bits;   /* LOCAL_PARTITIONING_FANOUT (:31), 1..12 */
+  uint32_t payload_bits;        /* PAYLOAD_BITS (:37); rid occupies network_fanout_bits+payload_bits bits */
+  uint32_t enable_two_level;    /* ENABLE_TWO_LEVEL_PARTITIONING (:28) */
+  uint32_t tuple_bytes;         /* 16 = data/Tuple.h:15-22 {u64 key; u64 rid};
+                                   8 = packed input, key in bits [32,64), rid in bits [0,32) */
+  uint32_t build_capacity;      /* tuples of one build slice held in shared memory: 0 = default (4096) */
+  double allocation_factor;     /* ALLOCATION_FACTOR (:35): receive-window head-room, >= 1.0 */
+  uint32_t chunk_tuples;        /* tuples per scheduled chunk of the scatter passes, 0 = default */
+  uint32_t flags;               /* RHJ_FLAG_* */
+} rhj_config;
+
+#define RHJ_FLAG_HIST_WARP_AGGREGATE 1u /* warp-aggregate the histogram atomics (skew-proof) */
+#define RHJ_FLAG_STAGE_HOST_INPUTS 2u    /* rhj_plan also reserves device staging for rhj_join_host */
+
+/* Join result: the reference only counts (HashJoin::RESULT_COUNTER, operators/HashJoin.cpp:28,
+ * tasks/BuildProbe.cpp:97-115).  The sums are an order-independent checksum over
+ * the matching (key, rid_R, rid_S) triples, all modulo 2^64. */
+typedef struct rhj_result {
+  uint64_t matches;
+  uint64_t sum_key;
+  uint64_t sum_rid_r;
+  uint64_t sum_rid_s;
+  uint64_t sum_mix;
+} rhj_result;
+
+/* Device timings of the last join, microseconds, under the reference's own keys
+ * (performance/Measurements.cpp:136-142, 246-268). */
+typedef struct rhj_timings {
+  double jtotal_us; /* JTOTAL */
+  double jhist_us;  /* JHIST: histograms + offsets */
+  double jmpi_us;   /* JMPI : network partitioning */
+  double jproc_us;  /* JPROC: local partitioning + build/probe */
+  double lp_us;     /* LPTASKTIME */
+  double bp_us;     /* BPTASKTIME */
+  double h2d_us;    /* host->device staging (rhj_join_host only), else 0 */
+} rhj_timings;
+
+/* Peer-visible description of a rank's receive windows (replaces MPI_Win_create,
+ * data/Window.cpp:35-45). */
+typedef struct rhj_window_handle {
+  unsigned char ipc[64]; /* cudaIpcMemHandle_t of the pool */
+  uint64_t inner_offset; /* byte offset of the inner-relation window inside the pool */
+  uint64_t outer_offset;
+  uint64_t capacity_inner; /* tuples */
+  uint64_t capacity_outer;
+} rhj_window_handle;
+
+const char *rhj_last_error(void);
+const char *rhj_version(void);
+/* kernels of this library launched by the calling process so far */
+uint64_t rhj_launch_count(void);
+
+/* ---- context + memory pool ------------------------------------------------
+ * rhj_init replaces HashJoin's constructor arguments (numberOfNodes, nodeId;
+ * operators/HashJoin.cpp:31-39) plus the Configuration knobs. */
+int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const rhj_config *cfg);
+int rhj_destroy(rhj_ctx *ctx);
+
+/* memory/Pool.cpp:25-38 Pool::allocate -> one cudaMalloc arena. */
+int rhj_pool_allocate(rhj_ctx *ctx, uint64_t bytes);
+/* memory/Pool.cpp:40-64 Pool::getMemory: bump allocation, 256-byte aligned (reference: 64). */
+int rhj_pool_get_memory(rhj_ctx *ctx, uint64_t bytes, void **out_dev);
+/* memory/Pool.cpp:76-79 Pool::reset */
+int rhj_pool_reset(rhj_ctx *ctx);
+/* memory/Pool.cpp:72-74 Pool::freeAll */
+int rhj_pool_free_all(rhj_ctx *ctx);
+/* Bytes the pool needs for rhj_plan() with these sizes (inputs not included). */
+uint64_t rhj_workspace_bytes(const rhj_config *cfg, int nranks, uint64_t max_local_inner,
+                             uint64_t max_local_outer, uint64_t window_inner_cap, uint64_t window_outer_cap);
+
+/* Carve windows and all intermediates out of the pool (allocating a pool of
+ * exactly the right size when none exists).  Nothing is allocated afterwards.
+ * window_*_cap = tuples this rank can receive per relation; 0 = allocation_factor * max_local_*.
+ * Replaces Window's constructor sizing (data/Window.cpp:16-50). */
+int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_local_outer, uint64_t window_inner_cap,
+             uint64_t window_outer_cap);
+
+/* ---- windows across ranks (MPI_Win_create / MPI_Put target resolution) --- */
+int rhj_window_export(rhj_ctx *ctx, rhj_window_handle *out);
+/* peer in another process: opens the CUDA IPC handle */
+int rhj_window_import(rhj_ctx *ctx, int peer_rank, const rhj_window_handle *handle);
+/* peer in this process (same or peer-enabled device): raw device pointers */
+int rhj_window_set_peer(rhj_ctx *ctx, int peer_rank, void *inner_window_dev, void *outer_window_dev);
+int rhj_window_get(rhj_ctx *ctx, void **inner_window_dev, void **outer_window_dev);
+
+/* ---- the four tasks (tasks/Task.h:10-30), individually invocable ---------- */
+
+/* TASK_HISTOGRAM part 1 -- histograms/LocalHistogram.cpp:35-53 for both relations.
+ * Leaves u64[2][P] (inner, outer) on the device: rhj_local_histogram_dev(). */
+int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *outer_dev, uint64_t outer_n,
+                  void *stream);
+uint64_t *rhj_local_histogram_dev(rhj_ctx *ctx);
+
+/* TASK_HISTOGRAM part 2 -- GlobalHistogram.cpp:31-48 (sum over ranks), AssignmentMap.cpp:34-49
+ * (p % nranks), OffsetMap.cpp:59-93 (base / relative / absolute offsets), all on the device.
+ * gathered_dev = u64[nranks][2][P], every rank's rhj_local_histogram_dev() in rank order
+ * (an all-gather replaces MPI_Allreduce + MPI_Exscan); NULL is allowed when nranks == 1. */
+int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, void *stream);
+
+/* tasks/HistogramComputation.cpp:78-130: the nine getters (host copies; synchronises `stream`).
+ * which: 0 inner, 1 outer.  Arrays have P = 1 << network_fanout_bits entries. */
+int rhj_get_assignment(rhj_ctx *ctx, uint32_t *out_host, void *stream);
+int rhj_get_local_histogram(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream);
+int rhj_get_global_histogram(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream);
+int rhj_get_base_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream);
+int rhj_get_write_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream);
+
+/* TASK_NET_PARTITION -- tasks/NetworkPartitioning.cpp:74-222 + data/Window.cpp:86-144:
+ * radix scatter on the low key bits with 16->8 byte compression, written straight
+ * into the owning rank's window (peer stores replace MPI_Put).  Uses the inputs
+ * given to rhj_histogram.  All ranks must finish (barrier) before the next stage. */
+int rhj_network_partition(rhj_ctx *ctx, void *stream);
+
+/* TASK_PARTITION -- tasks/LocalPartitioning.cpp:59-250 for every owned partition:
+ * histogram, 8-tuple padded prefix, scatter.  No-op unless enable_two_level. */
+int rhj_local_partition(rhj_ctx *ctx, void *stream);
+/* tasks/LocalPartitioning.cpp:138-192 results for owned partition `p` (host copies). */
+int rhj_get_local_partition(rhj_ctx *ctx, int which, uint32_t p, uint64_t *hist_host, uint64_t *prefix_host,
+                            void *stream);
+/* device address + tuple count of what LocalPartitioning wrote for owned partition p
+ * (count + 8 * L slots, as tasks/LocalPartitioning.cpp:79-81), or of the window partition itself. */
+int rhj_get_partition_dev(rhj_ctx *ctx, int which, uint32_t p, int after_local_pass, void **out_dev,
+                          uint64_t *out_tuples);
+
+/* TASK_BUILD_PROBE -- tasks/BuildProbe.cpp:47-121 for every (sub-)partition pair this rank owns. */
+int rhj_build_probe(rhj_ctx *ctx, void *stream);
+
+/* Result of this rank (HashJoin::RESULT_COUNTER + checksum); synchronises `stream`
+ * and reports device-side capacity errors. */
+int rhj_get_result(rhj_ctx *ctx, rhj_result *out, void *stream);
+int rhj_get_timings(rhj_ctx *ctx, rhj_timings *out);
+
+/* ---- the operator ------------------------------------------------------------
+ * HashJoin::join() for nranks == 1: all stages back to back on `stream`, no host
+ * synchronisation until the result is read.  Inputs are device-resident. */
+int rhj_join(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *outer_dev, uint64_t outer_n,
+             void *stream, rhj_result *out);
+/* Same, with HOST buffers: stages the relations through the pool (pinned-or-pageable
+ * host memory -> device) inside the call.  This is the end-to-end entry a reference
+ * user would bind in place of GPUWrapper / simple_hash_join_eth
+ * (tasks/gpu/GPUWrapper.cu:38-64, operators/gpu/eth.cuh:26-34). */
+int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host, uint64_t outer_n,
+                  void *stream, rhj_result *out);
+
+/* ---- relation generators on the device (data/Relation.cpp:63-85 stand-ins for sizes
+ * where host rand() Fisher-Yates is impractical; identical to oracle/orc_fill_perm) ---- */
+int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n, uint64_t first, uint64_t domain,
+                  uint64_t seed, uint64_t modulo, uint64_t start_key, uint64_t start_rid, void *stream);
+
+/* ---- small CUDA runtime conveniences so that a C / ctypes caller need not link cudart:
+ * pinned host buffers (what MPI_Alloc_mem is to the reference's windows, data/Window.cpp:35)
+ * and blocking copies. */
+int rhj_host_alloc(void **out_host, uint64_t bytes);
+int rhj_host_free(void *host);
+int rhj_memcpy_d2h(void *dst_host, const void *src_dev, uint64_t bytes);
+int rhj_memcpy_h2d(void *dst_dev, const void *src_host, uint64_t bytes);
+
+/* ---- host-side planning logic, usable without a GPU (tests, multi-rank launchers) ----
+ * AssignmentMap.cpp:34-49 and OffsetMap.cpp:59-93 on host arrays; locals = u64[nranks][P]. */
+void rhj_host_assignment(uint32_t nranks, uint32_t parts, uint32_t *assignment);
+void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32_t rank, uint32_t parts, uint64_t *global,
+                      uint64_t *base, uint64_t *rel, uint64_t *abs, uint64_t *window_sizes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RHJ_H_ */
