@@ -109,6 +109,7 @@ SYMBOLS = {
     "rhj_join": (_int, [_vp, _vp, _u64, _vp, _u64, _vp, _resp]),
     "rhj_join_host": (_int, [_vp, _vp, _u64, _vp, _u64, _vp, _resp]),
     "rhj_fill_perm": (_int, [_vp, _u32, _u64, _u64, _u64, _u64, _u64, _u64, _u64, _vp]),
+    "rhj_local_histogram_noalloc": (_int, [_vp, _u32, _u64, _u32, _vp, _vp]),
     "rhj_host_alloc": (_int, [C.POINTER(_vp), _u64]),
     "rhj_host_free": (_int, [_vp]),
     "rhj_memcpy_d2h": (_int, [_vp, _vp, _u64]),

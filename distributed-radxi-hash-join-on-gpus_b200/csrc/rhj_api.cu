@@ -919,3 +919,98 @@ extern "C" void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32
   if (window_sizes)
     for (uint32_t r = 0; r < nranks; ++r) window_sizes[r] = running[r];  // data/Window.cpp:168-178
 }
+
+// -----------------------------------------------------------------------------------
+// Local histogram for callers that must not allocate (see include/rhj.h).
+//
+// The per-chunk count matrix that rhj_histogram() keeps in the pool lives here in a
+// fixed array inside the library image instead, so this entry point never asks the
+// CUDA runtime for memory.  Every GPU that loads the library carries the array
+// (4 MiB + 256 B) until the process exits.  All calls on a device share it and it
+// keeps whatever the previous call left behind: the status word is cleared on the
+// caller's stream at the start of each call, the counts are overwritten before they
+// are read.  Two calls whose GPU work overlaps (different streams, or different host
+// threads) race on it.
+// -----------------------------------------------------------------------------------
+#include <mutex>
+
+#define RHJ_NOALLOC_MAX_CELLS (1u << 20) /* chunks x bins */
+#define RHJ_NOALLOC_HEADER_BYTES 256u
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RHJ_NOALLOC_HEADER_BYTES + RHJ_NOALLOC_MAX_CELLS * 4u];
+
+static constexpr int kNoallocMaxDevices = 64;
+static std::mutex g_noalloc_mutex;
+static unsigned char *g_noalloc_dev_ptr[kNoallocMaxDevices] = {};
+static int g_noalloc_sm_count[kNoallocMaxDevices] = {};
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address a
+// kernel can use; the device address is looked up once per device, with that device current.
+static int noalloc_scratch(unsigned char **out, int *sm_count) {
+  int dev = -1;
+  RHJ_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoallocMaxDevices) return fail(RHJ_ERR_INVALID, "device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_dev_ptr[dev]) {
+    void *p = nullptr;
+    RHJ_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    int sms = 0;
+    RHJ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    g_noalloc_sm_count[dev] = sms;
+    g_noalloc_dev_ptr[dev] = static_cast<unsigned char *>(p);
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  *sm_count = g_noalloc_sm_count[dev];
+  return RHJ_OK;
+}
+
+template <int TB>
+static int noalloc_histogram_launch(const void *tuples_dev, uint64_t n, uint32_t net_bits, uint32_t nchunks,
+                                    uint32_t *matrix, int *status, uint64_t *hist_out_dev, int sm_count,
+                                    cudaStream_t st) {
+  const uint32_t P = 1u << net_bits;
+  if (nchunks > 0) {
+    InputSource<TB> src{tuples_dev, P - 1, net_bits, 0};
+    ChunkMapFlat cm{n, kDefaultChunk, nchunks};
+    const uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, 4096 / P));
+    const uint32_t grid = std::min<uint32_t>(nchunks, (uint32_t)sm_count * 4);
+    k_histogram<InputSource<TB>, ChunkMapFlat, false>
+        <<<grid, kHistTPB, (size_t)P * nrep * 4, st>>>(src, cm, P, nrep, matrix, status);
+    RHJ_CHECK_LAUNCH("k_histogram(noalloc)");
+  }
+  dim3 grid((P + 31) / 32, 1);
+  k_colscan<32><<<grid, 32 * 32, 0, st>>>(matrix, P, nullptr, nchunks, hist_out_dev, status);
+  RHJ_CHECK_LAUNCH("k_colscan(noalloc)");
+  return RHJ_OK;
+}
+
+extern "C" int rhj_local_histogram_noalloc(const void *tuples_dev, uint32_t tuple_bytes, uint64_t n,
+                                           uint32_t network_fanout_bits, uint64_t *hist_out_dev, void *stream) {
+  if (tuple_bytes != 16 && tuple_bytes != 8) return fail(RHJ_ERR_INVALID, "tuple_bytes must be 16 or 8");
+  if (network_fanout_bits < 1 || network_fanout_bits > 12)
+    return fail(RHJ_ERR_INVALID, "network_fanout_bits %u outside [1,12]", network_fanout_bits);
+  if (!hist_out_dev) return fail(RHJ_ERR_INVALID, "hist_out_dev is NULL");
+  if (n && !tuples_dev) return fail(RHJ_ERR_INVALID, "tuples_dev is NULL");
+  if (reinterpret_cast<uintptr_t>(tuples_dev) & (tuple_bytes - 1))
+    return fail(RHJ_ERR_INVALID, "tuples must be %u-byte aligned", tuple_bytes);
+  const uint64_t nchunks = (n + kDefaultChunk - 1) / kDefaultChunk;
+  const uint64_t cells = nchunks << network_fanout_bits;
+  if (cells > RHJ_NOALLOC_MAX_CELLS)
+    return fail(RHJ_ERR_CAPACITY,
+                "rhj_local_histogram_noalloc: %llu tuples at %u radix bits need %llu scratch cells, the built-in "
+                "array holds %u (at most %llu tuples at this fan-out); use rhj_histogram for larger inputs",
+                (unsigned long long)n, network_fanout_bits, (unsigned long long)cells, RHJ_NOALLOC_MAX_CELLS,
+                (unsigned long long)(RHJ_NOALLOC_MAX_CELLS >> network_fanout_bits) * kDefaultChunk);
+  unsigned char *scratch = nullptr;
+  int sm_count = 0;
+  int rc = noalloc_scratch(&scratch, &sm_count);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int *status = reinterpret_cast<int *>(scratch);
+  uint32_t *matrix = reinterpret_cast<uint32_t *>(scratch + RHJ_NOALLOC_HEADER_BYTES);
+  RHJ_CUDA(cudaMemsetAsync(status, 0, sizeof(int), st));  // the only word that must start at zero
+  return tuple_bytes == 16
+             ? noalloc_histogram_launch<16>(tuples_dev, n, network_fanout_bits, (uint32_t)nchunks, matrix, status,
+                                            hist_out_dev, sm_count, st)
+             : noalloc_histogram_launch<8>(tuples_dev, n, network_fanout_bits, (uint32_t)nchunks, matrix, status,
+                                           hist_out_dev, sm_count, st);
+}

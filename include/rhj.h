@@ -191,6 +191,36 @@ int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const 
 int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n, uint64_t first, uint64_t domain,
                   uint64_t seed, uint64_t modulo, uint64_t start_key, uint64_t start_rid, void *stream);
 
+/* ---- local histogram without any allocation ----------------------------------------
+ * No counterpart in the reference (its GPU seam mallocs and frees on every call,
+ * operators/gpu/eth.cu:144-156, 228-230).
+ *
+ * Who needs it: an engine that has already handed all of the GPU's memory to its own
+ * buffer manager (a later cudaMalloc from a library would simply fail), and callers on a
+ * latency-critical path, where cudaMalloc/cudaFree may stall on everything else the
+ * device is doing.  Neither can use rhj_init + rhj_plan + rhj_histogram, which take
+ * their scratch from a cudaMalloc'ed pool.
+ *
+ * What it does: the same result as rhj_histogram for ONE relation -- u64[P] counts of
+ * key & (P-1), P = 1 << network_fanout_bits (histograms/LocalHistogram.cpp:35-53) --
+ * written to hist_out_dev (caller-owned device memory, P * 8 bytes).  The caller passes
+ * inputs and output; the per-chunk counters the kernels need live in a fixed
+ * 4 MiB + 256 B array inside the library, present on every GPU that loads the library
+ * until the process exits.  No cudaMalloc, cudaFree or other allocating call is made.
+ *
+ * Limits and rules:
+ *  - ceil(n / 65536) * P must not exceed 1,048,576 (e.g. 268,435,456 tuples at 8 radix
+ *    bits, 16,777,216 at 12); larger inputs are refused with RHJ_ERR_CAPACITY.
+ *  - runs on the calling thread's current device, on `stream`.
+ *  - the first call on each device looks up the array's device address; make that call
+ *    before starting any stream capture.
+ *  - all calls on a device share the array: calls whose GPU work can overlap (different
+ *    streams or host threads) race with each other; order them on one stream or
+ *    synchronise between them.  The array keeps the previous call's contents; the
+ *    entry point itself resets what has to start from zero. */
+int rhj_local_histogram_noalloc(const void *tuples_dev, uint32_t tuple_bytes, uint64_t n,
+                                uint32_t network_fanout_bits, uint64_t *hist_out_dev, void *stream);
+
 /* ---- small CUDA runtime conveniences so that a C / ctypes caller need not link cudart:
  * pinned host buffers (what MPI_Alloc_mem is to the reference's windows, data/Window.cpp:35)
  * and blocking copies. */
