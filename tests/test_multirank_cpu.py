@@ -1,0 +1,76 @@
+"""N>1 host logic on CPU: two processes over torch.distributed/gloo do what the ranks of a
+multi-GPU join do between kernels -- all-gather the per-rank histograms, derive global
+histogram / assignment / offsets from the gathered matrix -- and must agree with the oracle's
+(and hence the reference's MPI_Allreduce + MPI_Exscan) result."""
+import importlib
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, per, knobs, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = O.Config(*knobs)
+    P = 1 << cfg.net_bits
+    inner, outer = O.generate_reference(world, per, per)  # every rank regenerates; uses only its share
+    local = np.concatenate([O.local_histogram(inner[rank], cfg), O.local_histogram(outer[rank], cfg)])
+    t = torch.from_numpy(local.view(np.int64).copy())
+    gathered = torch.empty(world * 2 * P, dtype=torch.int64)
+    dist.all_gather_into_tensor(gathered, t)
+    mat = gathered.numpy().view(np.uint64).reshape(world, 2, P)
+    L = rhj.lib()
+    res = {}
+    for which, name in ((0, "inner"), (1, "outer")):
+        loc = np.ascontiguousarray(mat[:, which, :])
+        g, b, rel, ab = (np.zeros(P, np.uint64) for _ in range(4))
+        ws = np.zeros(world, np.uint64)
+        L.rhj_host_offsets(loc.ctypes.data, world, rank, P, g.ctypes.data, b.ctypes.data, rel.ctypes.data,
+                           ab.ctypes.data, ws.ctypes.data)
+        res[name + "_global"], res[name + "_base"], res[name + "_abs"], res[name + "_ws"] = g, b, ab, ws
+    # barrier + "result aggregation" as HashJoin/Measurements do (sum of per-rank counts)
+    mine = O.join(inner, outer, cfg)[rank].matches
+    tot = torch.tensor([mine], dtype=torch.int64)
+    dist.all_reduce(tot)
+    res["total"] = np.array([int(tot.item())], np.uint64)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), **res)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("knobs", [(5, 5, 27, 1), (8, 8, 24, 1)])
+def test_two_ranks_gloo_offsets(oracle, tmp_path, knobs):
+    import torch.multiprocessing as mp
+    world, per = 2, 30000
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, per, knobs, str(tmp_path)), nprocs=world, join=True)
+    cfg = oracle.Config(*knobs)
+    inner, outer = oracle.generate_reference(world, per, per)
+    for name, rel in (("inner", inner), ("outer", outer)):
+        pl = oracle.plan(np.stack([oracle.local_histogram(t, cfg) for t in rel]), world)
+        for r in range(world):
+            z = np.load(tmp_path / f"rank{r}.npz")
+            assert np.array_equal(z[name + "_global"], pl.global_)
+            assert np.array_equal(z[name + "_base"], pl.base)
+            assert np.array_equal(z[name + "_abs"], pl.abs_[r])
+            assert np.array_equal(z[name + "_ws"], pl.window_size)
+            assert int(z["total"][0]) == world * per

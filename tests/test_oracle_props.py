@@ -1,0 +1,77 @@
+"""Properties of the CPU oracle that do not need the reference: independent sort-merge
+join, closed forms of the unique 1:1 FK workload, generator bijection."""
+import numpy as np
+import pytest
+
+
+def test_perm_is_a_bijection(oracle):
+    for dom in (1, 2, 3, 17, 1000, 4096, 100003):
+        t = oracle.fill_perm(dom, 0, dom, seed=dom + 1)
+        assert np.array_equal(np.sort(t["key"]), np.arange(dom, dtype=np.uint64))
+        assert np.array_equal(t["rid"], np.arange(dom, dtype=np.uint64))
+
+
+def test_rng_is_glibc_rand(oracle):
+    """srand(1234); rand() first values of glibc's TYPE_3 generator."""
+    import ctypes
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(1234)
+    want = [libc.rand() for _ in range(16)]
+    g = oracle.Rng(1234)
+    assert [g.next() for _ in range(16)] == want
+
+
+@pytest.mark.parametrize("knobs", [(5, 5, 27, 1), (5, 5, 27, 0), (8, 8, 24, 1), (2, 3, 30, 1), (10, 6, 22, 1)])
+@pytest.mark.parametrize("nranks", [1, 2, 3])
+def test_unique_fk_closed_form(oracle, knobs, nranks):
+    per = 20000
+    inner, outer = oracle.generate_reference(nranks, per, per)
+    res = oracle.join(inner, outer, oracle.Config(*knobs))
+    G = nranks * per
+    m, sk, sr, ss, _ = oracle.total(res)
+    assert m == G
+    assert sk == sr == ss == G * (G - 1) // 2
+    P = 1 << knobs[0]
+    if P % nranks == 0 and G % P == 0:
+        # every partition holds exactly G/P tuples; rank r owns P/nranks of them
+        assert [r.matches for r in res] == [G // nranks] * nranks
+
+
+def test_join_equals_sort_merge_with_duplicates_and_misses(oracle):
+    rng = np.random.default_rng(1)
+    for knobs in ((3, 3, 29, 1), (3, 3, 29, 0), (6, 4, 26, 1)):
+        r = np.zeros(3000, oracle.TUPLE)
+        s = np.zeros(5000, oracle.TUPLE)
+        r["key"] = rng.integers(0, 700, len(r))
+        s["key"] = rng.integers(0, 1400, len(s))
+        r["rid"] = np.arange(len(r))
+        s["rid"] = np.arange(len(s)) + 12345
+        res = oracle.join([r], [s], oracle.Config(*knobs))
+        assert res[0].astuple() == oracle.bruteforce(r, s).astuple()
+        # three ranks, arbitrary split
+        res3 = oracle.join([r[:1000], r[1000:1500], r[1500:]], [s[:10], s[10:4000], s[4000:]], oracle.Config(*knobs))
+        assert oracle.total(res3) == oracle.bruteforce(r, s).astuple()
+
+
+def test_compressed_value_round_trip(oracle):
+    """rid = value & mask, key = ((value >> shift) << F_net) | p."""
+    cfg = oracle.Config(5, 5, 27, 1)
+    t = oracle.fill_perm(10000, 0, 1 << 30, seed=9, start_rid=77)
+    pl = oracle.plan(oracle.local_histogram(t, cfg)[None, :], 1)
+    win = oracle.network_partition([t], cfg, pl)[0]
+    keys, rids = [], []
+    for p in range(32):
+        part = win[int(pl.base[p]):int(pl.base[p] + pl.global_[p])]
+        keys.append(((part >> np.uint64(32)) << np.uint64(5)) | np.uint64(p))
+        rids.append(part & np.uint64(0xFFFFFFFF))
+    got = np.sort(np.stack([np.concatenate(keys), np.concatenate(rids)], 1), 0)
+    want = np.sort(np.stack([t["key"], t["rid"]], 1), 0)
+    assert np.array_equal(got, want)
+
+
+def test_empty_relations(oracle):
+    e = np.zeros(0, oracle.TUPLE)
+    t = oracle.fill_perm(100, 0, 100, seed=1)
+    for a, b in ((e, e), (e, t), (t, e)):
+        for tl in (0, 1):
+            assert oracle.join([a], [b], oracle.Config(3, 2, 29, tl))[0].astuple() == (0, 0, 0, 0, 0)
