@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -59,6 +60,7 @@ static constexpr int kMaxRanks = 64;
 static constexpr uint32_t kDefaultChunk = 1u << 16;
 static constexpr uint32_t kDefaultBuildCap = 4096;
 static constexpr uint64_t kAlign = 256;
+static constexpr uint64_t kItemSlack = 65536;  // work-list entries beyond one per sub-partition
 
 enum Ev { EV_START, EV_HIST, EV_NET, EV_LOCAL, EV_BP, EV_H2D0, EV_COUNT };
 
@@ -91,6 +93,8 @@ struct rhj_ctx {
   uint64_t *d_item_lstart = nullptr, *d_item_jcount = nullptr, *d_item_jstart = nullptr;
   unsigned long long *d_work = nullptr, *d_result = nullptr;
   int *d_status = nullptr;
+  ItemDesc *d_items = nullptr;
+  uint64_t items_cap = 0;
 
   // peers (data/Window.cpp: target of MPI_Put)
   uint64_t peer_window[2][kMaxRanks] = {};
@@ -105,6 +109,10 @@ struct rhj_ctx {
   cudaEvent_t ev[EV_COUNT] = {};
   bool ev_valid[EV_COUNT] = {};
   double h2d_us = 0;
+
+  // tuning knobs (environment: RHJ_SCATTER=legacy, RHJ_IPT_NET, RHJ_IPT_LOC, RHJ_BP=legacy)
+  bool tune_legacy_scatter = false, tune_legacy_bp = false;
+  int tune_ipt_net = 4, tune_ipt_loc = 8;
 };
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
@@ -167,6 +175,10 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
+  if (const char *e = getenv("RHJ_SCATTER")) c->tune_legacy_scatter = strcmp(e, "legacy") == 0;
+  if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
+  if (const char *e = getenv("RHJ_IPT_NET")) c->tune_ipt_net = atoi(e) == 8 ? 8 : 4;
+  if (const char *e = getenv("RHJ_IPT_LOC")) c->tune_ipt_loc = atoi(e) == 8 ? 8 : 4;
   *out = c;
   return RHJ_OK;
 }
@@ -271,6 +283,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   add(2 * NS * 4);                                 // sub_cnt
   add(NS * 8); add((uint64_t)nowned * 8); add(((uint64_t)nowned + 1) * 8);  // item_lstart, jcount, jstart
   add(8); add(5 * 8); add(4);                      // work counter, result, status
+  add((NS + kItemSlack) * sizeof(ItemDesc));       // expanded build/probe work list
   lay->total = total;
 }
 
@@ -350,6 +363,8 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (!rc) rc = carve(ctx, 1ull, &ctx->d_work);
   if (!rc) rc = carve(ctx, 5ull, &ctx->d_result);
   if (!rc) rc = carve(ctx, 1ull, &ctx->d_status);
+  ctx->items_cap = NS + kItemSlack;
+  if (!rc) rc = carve(ctx, ctx->items_cap, &ctx->d_items);
   if (rc) return rc;
   RHJ_CUDA(cudaMemset(ctx->d_status, 0, sizeof(int)));
   RHJ_CUDA(cudaMemset(ctx->d_result, 0, 5 * 8));
@@ -435,10 +450,31 @@ static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint
   return RHJ_OK;
 }
 
+template <class Source, class Map, int IPT>
+static int launch_scatter_tma(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+                              const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+  size_t smem = scatter_tma_smem_bytes<Source, IPT>(nbins);
+  auto kern = k_scatter_tma<Source, Map, IPT>;
+  RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScatTPB, smem));
+  if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
+  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count * per_sm));
+  kern<<<grid, kScatTPB, smem, st>>>(src, cm, nbins, chunk_off, bin_base, ctx->d_status);
+  RHJ_CHECK_LAUNCH("k_scatter_tma");
+  return RHJ_OK;
+}
+
 template <class Source, class Map>
 static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                          const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+                          const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st, int ipt) {
   if (grid_chunks == 0) return RHJ_OK;
+  if (!ctx->tune_legacy_scatter) {
+    // wide fan-outs need the shared memory for the per-bin arrays: fall back to the smaller tile
+    if (ipt == 8 && scatter_tma_smem_bytes<Source, 8>(nbins) <= 110 * 1024)
+      return launch_scatter_tma<Source, Map, 8>(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
+    return launch_scatter_tma<Source, Map, 4>(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
+  }
   size_t smem = scatter_smem_bytes(nbins);
   RHJ_CUDA(cudaFuncSetAttribute(k_scatter<Source, Map>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 2);
@@ -543,10 +579,10 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
     int rc;
     if (ctx->cfg.tuple_bytes == 16) {
       InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
     } else {
       InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
     }
     if (rc) return rc;
   }
@@ -614,7 +650,7 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
       ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
                      ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
       rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k],
-                          ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
+                          ctx->d_sub_addr + (uint64_t)k * ctx->NS, st, ctx->tune_ipt_loc);
       if (rc) return rc;
     }
   }
@@ -626,6 +662,15 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
 
 template <int CAP>
 static int launch_build_probe(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_t st) {
+  if (!ctx->tune_legacy_bp) {
+    k_expand_items<CAP><<<(a.NS + 255) / 256, 256, 0, st>>>(a, ctx->d_items);
+    RHJ_CHECK_LAUNCH("k_expand_items");
+    size_t smem2 = build_probe2_smem_bytes<CAP>();
+    RHJ_CUDA(cudaFuncSetAttribute(k_build_probe2<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    k_build_probe2<CAP><<<ctx->sm_count, kBp2TPB, smem2, st>>>(a);
+    RHJ_CHECK_LAUNCH("k_build_probe2");
+    return RHJ_OK;
+  }
   size_t smem = build_probe_smem_bytes<CAP>();
   RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
@@ -664,6 +709,8 @@ extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) {
     a.shift_bits = ctx->shift_bits;
     a.sslice = ctx->sslice;
     a.status = ctx->d_status;
+    a.items = ctx->d_items;
+    a.items_cap = ctx->items_cap;
     int rc;
     switch (ctx->cap_r) {
       case 1024: rc = launch_build_probe<1024>(ctx, a, st); break;

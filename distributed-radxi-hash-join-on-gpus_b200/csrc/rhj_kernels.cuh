@@ -66,9 +66,27 @@ struct ChunkMapSeg {  // one segment per owned network partition (chunks never s
 // tuple sources
 // ---------------------------------------------------------------------------------
 template <int TB>
+struct RawOf { using type = uint64_t; };
+template <>
+struct RawOf<16> { using type = ulonglong2; };
+
+template <int TB>
 struct InputSource {  // pass 1: Tuple -> (compressed value, key & (P-1))
   const void *data;
   uint32_t mask, net_bits, key_shift;
+  using Raw = typename RawOf<TB>::type;  // what one input element looks like in memory
+  static constexpr bool kDigitFromValue = false;
+  __device__ __forceinline__ const void *base() const { return data; }
+  __device__ __forceinline__ void decode(const ulonglong2 &r, uint64_t &value, uint32_t &dg) const {
+    dg = (uint32_t)r.x & mask;
+    value = compress_tuple(r.x, r.y, net_bits, key_shift);
+  }
+  __device__ __forceinline__ void decode(const uint64_t &r, uint64_t &value, uint32_t &dg) const {
+    const uint64_t key = r >> 32, rid = r & 0xFFFFFFFFull;
+    dg = (uint32_t)key & mask;
+    value = compress_tuple(key, rid, net_bits, key_shift);
+  }
+  __device__ __forceinline__ uint32_t digit_of_value(uint64_t) const { return 0; }
   __device__ __forceinline__ uint32_t digit(uint64_t i) const {
     return (uint32_t)InputTuple<TB>::load_key(data, i) & mask;
   }
@@ -83,6 +101,14 @@ struct InputSource {  // pass 1: Tuple -> (compressed value, key & (P-1))
 struct ValueSource {  // pass 2: CompressedTuple, digit = bits [key_shift, key_shift + loc_bits)
   const uint64_t *data;
   uint32_t shift, mask;
+  using Raw = uint64_t;
+  static constexpr bool kDigitFromValue = true;
+  __device__ __forceinline__ const void *base() const { return data; }
+  __device__ __forceinline__ void decode(const uint64_t &r, uint64_t &value, uint32_t &dg) const {
+    value = r;
+    dg = (uint32_t)(r >> shift) & mask;
+  }
+  __device__ __forceinline__ uint32_t digit_of_value(uint64_t v) const { return (uint32_t)(v >> shift) & mask; }
   __device__ __forceinline__ uint32_t digit(uint64_t i) const {
     return (uint32_t)(ld_stream_u64(data + i) >> shift) & mask;
   }
@@ -409,6 +435,174 @@ __global__ void __launch_bounds__(kScatTPB, 2) k_scatter(Source src, Map cm, uin
 }
 
 // ---------------------------------------------------------------------------------
+// K2 / K3, pipelined: same tile algorithm as k_scatter, but the input tile is brought
+// into shared memory by a bulk asynchronous copy (TMA, cp.async.bulk -> UBLKCP) that
+// completes on an mbarrier.  Two input stages: while tile k is ranked / placed /
+// written, the copy of tile k+1 is in flight, and as soon as tile k is written out its
+// stage is refilled with tile k+2 -- global-load latency never sits on the critical
+// path and no registers are held across it.  The stage that held tile k's input is
+// reused as its output staging buffer (8 bytes per tuple <= the input it replaces).
+// ---------------------------------------------------------------------------------
+template <class Source, int IPT>
+__host__ __device__ inline size_t scatter_tma_smem_bytes(uint32_t nbins) {
+  constexpr size_t T = (size_t)kScatTPB * IPT;
+  constexpr size_t stage = T * sizeof(typename Source::Raw) + 16;  // +16: a misaligned first element
+  return 2 * stage + (size_t)nbins * (8 + 8 + 4 + 4) + 64 * 4 + (Source::kDigitFromValue ? 0 : T * 2) + 2 * 8 + 128;
+}
+
+template <class Source, class Map, int IPT>
+__global__ void __launch_bounds__(kScatTPB, (IPT <= 4 ? 3 : 2))
+    k_scatter_tma(Source src, Map cm, uint32_t nbins, const uint32_t *__restrict__ chunk_off,
+                  const uint64_t *__restrict__ bin_base, const int *__restrict__ status) {
+  using Raw = typename Source::Raw;
+  constexpr uint32_t T = kScatTPB * IPT;
+  constexpr uint32_t RAWB = sizeof(Raw);
+  constexpr uint32_t STAGE_BYTES = T * RAWB + 16;
+  extern __shared__ __align__(128) unsigned char sh_raw[];
+  if (*status != kDevOk) return;
+  unsigned char *in_stage[2] = {sh_raw, sh_raw + STAGE_BYTES};
+  uint64_t *delta = reinterpret_cast<uint64_t *>(sh_raw + 2 * STAGE_BYTES);
+  uint64_t *cursor = delta + nbins;
+  uint64_t *bars = cursor + nbins;  // [2]
+  uint32_t *cnt = reinterpret_cast<uint32_t *>(bars + 2);
+  uint32_t *start = cnt + nbins;
+  uint32_t *tmp = start + nbins;
+  uint16_t *dig = reinterpret_cast<uint16_t *>(tmp + 64);
+
+  const uint32_t tid = threadIdx.x;
+  const uint32_t nchunks = cm.count();
+  const unsigned char *gbase = static_cast<const unsigned char *>(src.base());
+
+  struct TileIt {
+    uint32_t c, seg;
+    uint64_t e, t0;
+    bool valid;
+  };
+  auto open_chunk = [&](TileIt &it, uint32_t c) {
+    it.c = c;
+    it.valid = c < nchunks;
+    if (it.valid) {
+      uint64_t b;
+      cm.range(c, b, it.e, it.seg);
+      it.t0 = b;
+    }
+  };
+  auto advance = [&](TileIt &it) {
+    if (!it.valid) return;
+    it.t0 += T;
+    if (it.t0 >= it.e) open_chunk(it, it.c + gridDim.x);
+  };
+  // thread 0: start the bulk copy of the tile `it` points at into stage s
+  auto issue = [&](const TileIt &it, uint32_t s) {
+    const uint64_t n = (it.e - it.t0) < (uint64_t)T ? (it.e - it.t0) : (uint64_t)T;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(gbase) + it.t0 * RAWB;
+    const uintptr_t a0 = a & ~uintptr_t(15), a1 = (a + n * RAWB) & ~uintptr_t(15);
+    if (a1 > a0) {
+      mbar_arrive_expect_tx(&bars[s], (uint32_t)(a1 - a0));
+      bulk_g2s(in_stage[s], reinterpret_cast<const void *>(a0), (uint32_t)(a1 - a0), &bars[s]);
+    } else {
+      mbar_arrive(&bars[s]);
+    }
+  };
+
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_fence_init();
+  }
+  for (uint32_t d = tid; d < nbins; d += kScatTPB) cnt[d] = 0;
+  __syncthreads();
+
+  TileIt cur, nxt;
+  open_chunk(cur, blockIdx.x);
+  nxt = cur;
+  if (cur.valid && tid == 0) issue(cur, 0);
+  advance(nxt);
+  if (nxt.valid && tid == 0) issue(nxt, 1);
+
+  uint32_t s = 0, phase0 = 0, phase1 = 0, cur_chunk = 0xFFFFFFFFu;
+  while (cur.valid) {
+    if (cur.c != cur_chunk) {  // first tile of a chunk: this chunk's write cursors
+      cur_chunk = cur.c;
+      for (uint32_t d = tid; d < nbins; d += kScatTPB)
+        cursor[d] = bin_base[(uint64_t)cur.seg * nbins + d] + (uint64_t)chunk_off[(uint64_t)cur.c * nbins + d] * 8;
+      __syncthreads();
+    }
+    const uint32_t tile_n = (cur.e - cur.t0) < (uint64_t)T ? (uint32_t)(cur.e - cur.t0) : T;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(gbase) + cur.t0 * RAWB;
+    const uint32_t skip = (uint32_t)(a & 15);                       // bytes copied in front of element 0
+    const bool tail_direct = ((a + (uint64_t)tile_n * RAWB) & 15) != 0;  // last element is not in the copy
+    const unsigned char *in = in_stage[s] + skip;
+
+    mbar_wait(&bars[s], s ? phase1 : phase0);
+    if (s) phase1 ^= 1; else phase0 ^= 1;
+
+    uint64_t val[IPT];
+    uint32_t dg[IPT], rk[IPT];
+#pragma unroll
+    for (int u = 0; u < IPT; ++u) {
+      const uint32_t i = u * kScatTPB + tid;
+      dg[u] = kInvalidDigit;
+      if (i < tile_n) {
+        Raw r;
+        if (tail_direct && i == tile_n - 1) r = *reinterpret_cast<const Raw *>(a + (uint64_t)i * RAWB);
+        else r = *reinterpret_cast<const Raw *>(in + (size_t)i * RAWB);
+        src.decode(r, val[u], dg[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < IPT; ++u)
+      if (dg[u] != kInvalidDigit) rk[u] = atomicAdd(&cnt[dg[u]], 1u);
+    __syncthreads();  // every thread has its input in registers: the stage may be overwritten
+
+    uint32_t carry = 0;
+    for (uint32_t d0 = 0; d0 < nbins; d0 += kScatTPB) {
+      const uint32_t d = d0 + tid;
+      const uint32_t v = d < nbins ? cnt[d] : 0;
+      uint32_t total;
+      const uint32_t ex = block_exclusive_scan<uint32_t>(v, tmp, &total);
+      if (d < nbins) {
+        const uint32_t st = carry + ex;
+        const uint64_t cu = cursor[d];
+        start[d] = st;
+        delta[d] = cu - (uint64_t)st * 8;
+        cursor[d] = cu + (uint64_t)v * 8;
+        cnt[d] = 0;
+      }
+      carry += total;
+    }
+    __syncthreads();
+
+    uint64_t *stage = reinterpret_cast<uint64_t *>(in_stage[s]);
+#pragma unroll
+    for (int u = 0; u < IPT; ++u) {
+      if (dg[u] != kInvalidDigit) {
+        const uint32_t pos = start[dg[u]] + rk[u];
+        stage[pos] = val[u];
+        if (!Source::kDigitFromValue) dig[pos] = (uint16_t)dg[u];
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < IPT; ++u) {
+      const uint32_t i = u * kScatTPB + tid;
+      if (i < tile_n) {
+        const uint64_t v = stage[i];
+        const uint32_t d = Source::kDigitFromValue ? src.digit_of_value(v) : (uint32_t)dig[i];
+        st_stream_u64(reinterpret_cast<uint64_t *>(delta[d] + (uint64_t)i * 8), v);
+      }
+    }
+    fence_proxy_async_smem();  // generic accesses to this stage happen-before the next bulk copy into it
+    __syncthreads();
+
+    advance(nxt);
+    if (nxt.valid && tid == 0) issue(nxt, s);
+    advance(cur);
+    s ^= 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------
 // Kq: after the local-pass histogram.  One block per owned partition j:
 //   sub_cnt[k][j][l]  (from k_colscan totals)  ->  LocalPartitioning.cpp:165-192:
 //   prefix[l] = sum_{l'<l} roundup8(cnt[l']);  output region of partition j starts at
@@ -515,7 +709,62 @@ struct BuildProbeArgs {
   uint32_t net_bits, key_shift, shift_bits;
   uint32_t sslice;
   const int *status;
+  const struct ItemDesc *items;  // [items_cap] expanded work list (k_expand_items)
+  uint64_t items_cap;
 };
+
+// One build/probe work item, fully resolved: what a CTA needs to start its loads.
+struct __align__(16) ItemDesc {
+  uint64_t r_off, s_off;  // tuple index into src[0] / src[1]
+  uint32_t r_n, s_n;
+  uint32_t partition, pad;
+};
+
+// Resolve item -> (sub-partition, build slice, probe slice) by searching the two-level
+// item prefix (used to expand the list, and directly for items beyond the list's capacity).
+template <int CAP, class Search>
+__device__ __forceinline__ ItemDesc resolve_item(const BuildProbeArgs &a, uint64_t item, Search search) {
+  const uint32_t j = search(a.item_jstart, a.nowned, item);
+  const uint64_t local = item - a.item_jstart[j];
+  const uint32_t l = search(a.item_lstart + (uint64_t)j * a.L, a.L, local);
+  const uint32_t sp = j * a.L + l;
+  const uint32_t q = (uint32_t)(local - a.item_lstart[sp]);
+  const uint32_t cnt_r = a.sub_cnt[sp], cnt_s = a.sub_cnt[a.NS + sp];
+  const uint32_t s_slices = (cnt_s + a.sslice - 1) / a.sslice;
+  const uint32_t ri = q / s_slices, si = q % s_slices;
+  ItemDesc d;
+  d.r_off = a.sub_off[sp] + (uint64_t)ri * CAP;
+  d.s_off = a.sub_off[a.NS + sp] + (uint64_t)si * a.sslice;
+  d.r_n = min((uint32_t)CAP, cnt_r - ri * CAP);
+  d.s_n = min(a.sslice, cnt_s - si * a.sslice);
+  d.partition = a.rank + j * a.nranks;
+  d.pad = 0;
+  return d;
+}
+
+// Expand the work list: one thread per sub-partition writes the descriptors of its items.
+template <int CAP>
+__global__ void __launch_bounds__(256) k_expand_items(BuildProbeArgs a, ItemDesc *__restrict__ out) {
+  const uint32_t sp = blockIdx.x * blockDim.x + threadIdx.x;
+  if (sp >= a.NS) return;
+  const uint32_t j = sp / a.L;
+  const uint32_t cnt_r = a.sub_cnt[sp], cnt_s = a.sub_cnt[a.NS + sp];
+  if (cnt_r == 0 || cnt_s == 0) return;
+  const uint32_t r_slices = (cnt_r + CAP - 1) / CAP, s_slices = (cnt_s + a.sslice - 1) / a.sslice;
+  uint64_t idx = a.item_jstart[j] + a.item_lstart[sp];
+  for (uint32_t ri = 0; ri < r_slices; ++ri)
+    for (uint32_t si = 0; si < s_slices; ++si, ++idx) {
+      if (idx >= a.items_cap) return;
+      ItemDesc d;
+      d.r_off = a.sub_off[sp] + (uint64_t)ri * CAP;
+      d.s_off = a.sub_off[a.NS + sp] + (uint64_t)si * a.sslice;
+      d.r_n = min((uint32_t)CAP, cnt_r - ri * CAP);
+      d.s_n = min(a.sslice, cnt_s - si * a.sslice);
+      d.partition = a.rank + j * a.nranks;
+      d.pad = 0;
+      out[idx] = d;
+    }
+}
 
 template <int CAP>
 __host__ __device__ constexpr size_t build_probe_smem_bytes() {
@@ -646,6 +895,195 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
     unsigned long long s = 0;
     for (int w = 0; w < kBpTPB / 32; ++w) s += s_red[tid][w];
     if (s) atomicAdd(&a.result[tid], s);
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// K4, pipelined.  One CTA of 1024 threads per SM, items assigned round-robin.  The
+// loads of item i+1 are started before item i is processed: its build slice by one bulk
+// asynchronous copy (TMA) straight into the second table buffer, the first 4096 probe
+// tuples into registers; its descriptor was fetched one item earlier still.  Build and
+// probe of item i therefore run entirely out of shared memory / registers while the
+// memory system streams the next item.
+// ---------------------------------------------------------------------------------
+constexpr int kBp2TPB = 1024;
+constexpr int kBp2SV = 2;                          // 16-byte probe vectors per thread per batch
+constexpr int kBp2Batch = kBp2TPB * kBp2SV * 2;    // probe tuples per batch
+
+template <int CAP>
+__host__ __device__ constexpr size_t build_probe2_smem_bytes() {
+  return (size_t)CAP * (8 + 8 + 4 + 2) + 64;
+}
+
+template <int CAP>
+__global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
+  extern __shared__ __align__(128) unsigned char sh_raw[];
+  __shared__ unsigned long long s_red[5][kBp2TPB / 32];
+  if (*a.status != kDevOk) return;
+  uint64_t *tup[2] = {reinterpret_cast<uint64_t *>(sh_raw), reinterpret_cast<uint64_t *>(sh_raw) + CAP};
+  uint32_t *bucket = reinterpret_cast<uint32_t *>(tup[1] + CAP);
+  uint16_t *next = reinterpret_cast<uint16_t *>(bucket + CAP);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(next + CAP);
+  const uint32_t tid = threadIdx.x;
+  const uint64_t rid_mask = a.key_shift >= 64 ? ~0ull : ((1ull << a.key_shift) - 1);
+  const uint64_t total = a.item_jstart[a.nowned];
+  const uint64_t stride = gridDim.x;
+
+  auto fetch = [&](uint64_t item) -> ItemDesc {
+    if (item < a.items_cap) {
+      const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(a.items + item);
+      ulonglong2 lo = p[0], hi = p[1];
+      ItemDesc d;
+      d.r_off = lo.x;
+      d.s_off = lo.y;
+      d.r_n = (uint32_t)hi.x;
+      d.s_n = (uint32_t)(hi.x >> 32);
+      d.partition = (uint32_t)hi.y;
+      d.pad = 0;
+      return d;
+    }
+    return resolve_item<CAP>(a, item, [](const uint64_t *arr, uint32_t n, uint64_t x) { return warp_upper_bound(arr, n, x); });
+  };
+  // start the loads of an item's build slice into table buffer `t`
+  auto issue_build = [&](const ItemDesc &d, uint64_t *t, uint64_t *bar) {
+    const uint64_t *rp = a.src[0] + d.r_off;
+    const uint32_t nbulk = (reinterpret_cast<uintptr_t>(rp) & 15) == 0 ? (d.r_n & ~1u) : 0u;
+    if (tid == 0) {
+      if (nbulk) {
+        mbar_arrive_expect_tx(bar, nbulk * 8);
+        bulk_g2s(t, rp, nbulk * 8, bar);
+      } else {
+        mbar_arrive(bar);
+      }
+    }
+    for (uint32_t i = nbulk + tid; i < d.r_n; i += kBp2TPB) t[i] = ld_stream_u64(rp + i);  // odd tail / unaligned slice
+  };
+  // probe-side addressing: [head scalar][nv 16-byte vectors][tail scalar]
+  auto probe_shape = [&](const ItemDesc &d, const uint64_t *&sp, uint32_t &head, uint32_t &nv) {
+    sp = a.src[1] + d.s_off;
+    head = (reinterpret_cast<uintptr_t>(sp) & 8) ? 1u : 0u;
+    if (head > d.s_n) head = d.s_n;
+    nv = (d.s_n - head) >> 1;
+  };
+  auto load_batch = [&](const uint64_t *sp, uint32_t head, uint32_t nv, uint32_t batch, ulonglong2 (&x)[kBp2SV]) {
+    const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(sp + head);
+#pragma unroll
+    for (int u = 0; u < kBp2SV; ++u) {
+      const uint32_t i = batch * (kBp2TPB * kBp2SV) + u * kBp2TPB + tid;
+      if (i < nv) x[u] = ld_stream_v2(v2 + i);
+    }
+  };
+
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  uint64_t id = blockIdx.x;
+  bool v_cur = id < total, v_n1 = id + stride < total, v_n2 = false;
+  ItemDesc cur{}, n1{}, n2{};
+  ulonglong2 xs_cur[kBp2SV], xs_n1[kBp2SV];
+  if (v_cur) cur = fetch(id);
+  if (v_n1) n1 = fetch(id + stride);
+  if (v_cur) {
+    issue_build(cur, tup[0], &bars[0]);
+    const uint64_t *sp;
+    uint32_t head, nv;
+    probe_shape(cur, sp, head, nv);
+    load_batch(sp, head, nv, 0, xs_cur);
+  }
+
+  uint64_t acc_n = 0, acc_key = 0, acc_rr = 0, acc_rs = 0, acc_mix = 0;
+  uint32_t s = 0, phase0 = 0, phase1 = 0;
+  while (v_cur) {
+    v_n2 = id + 2 * stride < total;
+    if (v_n2) n2 = fetch(id + 2 * stride);  // needed only at the bottom of the loop
+    if (v_n1) {
+      issue_build(n1, tup[s ^ 1], &bars[s ^ 1]);
+      const uint64_t *sp;
+      uint32_t head, nv;
+      probe_shape(n1, sp, head, nv);
+      load_batch(sp, head, nv, 0, xs_n1);
+    }
+    uint32_t nb = 1;
+    while (nb < cur.r_n) nb <<= 1;
+    const uint32_t hmask = nb - 1;
+    for (uint32_t i = tid; i < nb; i += kBp2TPB) bucket[i] = 0;
+    __syncthreads();
+    mbar_wait(&bars[s], s ? phase1 : phase0);
+    if (s) phase1 ^= 1; else phase0 ^= 1;
+
+    // ---- build (BuildProbe.cpp:82-86) ----
+    const uint64_t *t = tup[s];
+    for (uint32_t i = tid; i < cur.r_n; i += kBp2TPB) {
+      const uint32_t idx = (uint32_t)(t[i] >> a.shift_bits) & hmask;
+      next[i] = (uint16_t)atomicExch(&bucket[idx], i + 1);
+    }
+    __syncthreads();
+
+    // ---- probe (BuildProbe.cpp:97-106) ----
+    {
+      const uint32_t partition = cur.partition;
+      auto probe = [&](uint64_t v) {
+        const uint64_t kpart = v >> a.key_shift;
+        uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
+        while (hit) {
+          const uint64_t r = t[hit - 1];
+          if ((r >> a.key_shift) == kpart) {
+            const uint64_t key = (kpart << a.net_bits) | partition;
+            const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
+            acc_n += 1;
+            acc_key += key;
+            acc_rr += rid_r;
+            acc_rs += rid_s;
+            acc_mix += mix_triple(key, rid_r, rid_s);
+          }
+          hit = next[hit - 1];
+        }
+      };
+      const uint64_t *sp;
+      uint32_t head, nv;
+      probe_shape(cur, sp, head, nv);
+      if (tid == 0 && head) probe(ld_stream_u64(sp));
+      if (tid == 1 && ((cur.s_n - head) & 1)) probe(ld_stream_u64(sp + cur.s_n - 1));
+      const uint32_t nbatch = (nv + kBp2TPB * kBp2SV - 1) / (kBp2TPB * kBp2SV);
+      for (uint32_t b = 0; b < nbatch; ++b) {
+        if (b > 0) load_batch(sp, head, nv, b, xs_cur);
+#pragma unroll
+        for (int u = 0; u < kBp2SV; ++u) {
+          const uint32_t i = b * (kBp2TPB * kBp2SV) + u * kBp2TPB + tid;
+          if (i < nv) {
+            probe(xs_cur[u].x);
+            probe(xs_cur[u].y);
+          }
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    cur = n1;
+#pragma unroll
+    for (int u = 0; u < kBp2SV; ++u) xs_cur[u] = xs_n1[u];
+    v_cur = v_n1;
+    n1 = n2;
+    v_n1 = v_n2;
+    id += stride;
+    s ^= 1;
+  }
+
+  uint64_t v[5] = {acc_n, acc_key, acc_rr, acc_rs, acc_mix};
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    uint64_t w = warp_sum(v[k]);
+    if ((tid & 31) == 0) s_red[k][tid >> 5] = w;
+  }
+  __syncthreads();
+  if (tid < 5) {
+    unsigned long long sum = 0;
+    for (int w = 0; w < kBp2TPB / 32; ++w) sum += s_red[tid][w];
+    if (sum) atomicAdd(&a.result[tid], sum);
   }
 }
 
