@@ -83,6 +83,9 @@ struct rhj_ctx {
   void *staged_input[2] = {nullptr, nullptr};
   uint32_t *chunk1_hist[2] = {nullptr, nullptr};
   uint32_t *chunk2_hist[2] = {nullptr, nullptr};
+  uint32_t *tile1_off[2] = {nullptr, nullptr}, *tile2_off[2] = {nullptr, nullptr};    // [row][bins]
+  uint16_t *tile1_start[2] = {nullptr, nullptr}, *tile2_start[2] = {nullptr, nullptr};
+  uint32_t tiles_per_chunk = 0;
   uint64_t *d_local_hist = nullptr, *d_global = nullptr, *d_base = nullptr, *d_rel = nullptr, *d_abs = nullptr,
            *d_dest = nullptr, *d_winsizes = nullptr;
   uint32_t *d_assign = nullptr;
@@ -111,8 +114,9 @@ struct rhj_ctx {
   double h2d_us = 0;
 
   // tuning knobs (environment: RHJ_SCATTER=legacy, RHJ_IPT_NET, RHJ_IPT_LOC, RHJ_BP=legacy)
-  bool tune_legacy_scatter = false, tune_legacy_bp = false;
-  int tune_ipt_net = 4, tune_ipt_loc = 8;
+  int tune_scatter = 2;  // 0 legacy, 1 TMA-staged input, 2 offset-driven (default)
+  bool tune_legacy_bp = false;
+  int tune_ipt_net = 4, tune_ipt_loc = 8, tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4;
 };
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
@@ -171,11 +175,15 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   c->chunk1 = c->chunk2 = cfg->chunk_tuples ? cfg->chunk_tuples : kDefaultChunk;
   c->cap_r = cfg->build_capacity ? cfg->build_capacity : kDefaultBuildCap;
   c->sslice = 4 * c->cap_r;
+  c->tiles_per_chunk = c->chunk1 / kScatTile;
   cudaDeviceProp prop;
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
-  if (const char *e = getenv("RHJ_SCATTER")) c->tune_legacy_scatter = strcmp(e, "legacy") == 0;
+  if (const char *e = getenv("RHJ_SCATTER")) c->tune_scatter = strcmp(e, "legacy") == 0 ? 0 : strcmp(e, "tma") == 0 ? 1 : 2;
+  if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
+  if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = std::max(0, std::min(32, atoi(e)));
+  if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
   if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
   if (const char *e = getenv("RHJ_IPT_NET")) c->tune_ipt_net = atoi(e) == 8 ? 8 : 4;
   if (const char *e = getenv("RHJ_IPT_LOC")) c->tune_ipt_loc = atoi(e) == 8 ? 8 : 4;
@@ -273,6 +281,13 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
     if (cfg->flags & RHJ_FLAG_STAGE_HOST_INPUTS) add(max_local[k] * cfg->tuple_bytes);
     add((uint64_t)lay->max_chunks1[k] * P * 4);
     if (cfg->enable_two_level) add((uint64_t)lay->max_chunks2[k] * L * 4);
+    const uint64_t tpc = chunk / kScatTile;
+    add((uint64_t)lay->max_chunks1[k] * tpc * P * 4);
+    add((uint64_t)lay->max_chunks1[k] * tpc * P * 2);
+    if (cfg->enable_two_level) {
+      add((uint64_t)lay->max_chunks2[k] * tpc * L * 4);
+      add((uint64_t)lay->max_chunks2[k] * tpc * L * 2);
+    }
   }
   for (int i = 0; i < 6; ++i) add(2ull * P * 8);   // local, global, base, rel, abs, dest
   add((uint64_t)P * 4);                            // assignment
@@ -340,6 +355,11 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
     }
     if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * P, &ctx->chunk1_hist[k]);
     if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * L, &ctx->chunk2_hist[k]);
+    const uint64_t tpc = ctx->tiles_per_chunk;
+    if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_off[k]);
+    if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_start[k]);
+    if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_off[k]);
+    if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_start[k]);
   }
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_local_hist);
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_global);
@@ -436,8 +456,18 @@ static int record(rhj_ctx *ctx, int which, cudaStream_t st) {
 
 template <class Source, class Map>
 static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                            uint32_t *chunk_hist, cudaStream_t st) {
+                            uint32_t *chunk_hist, uint32_t *tile_off, uint16_t *tile_start, cudaStream_t st) {
   if (grid_chunks == 0) return RHJ_OK;
+  if (ctx->tune_scatter == 2) {
+    // few replicas: every replica has to be summed per tile, and 256 random bins rarely collide
+    uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, (256u * ctx->tune_hist_rep) / nbins));
+    size_t smem = ((size_t)2 * nbins * nrep + nbins + 80) * 4;
+    uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 4);
+    k_histogram_tiles<Source, Map><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, ctx->tiles_per_chunk, chunk_hist,
+                                                                  tile_off, tile_start, ctx->d_status);
+    RHJ_CHECK_LAUNCH("k_histogram_tiles");
+    return RHJ_OK;
+  }
   const bool agg = (ctx->cfg.flags & RHJ_FLAG_HIST_WARP_AGGREGATE) != 0;
   uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, 4096 / nbins));
   size_t smem = (size_t)nbins * nrep * 4;
@@ -465,11 +495,33 @@ static int launch_scatter_tma(rhj_ctx *ctx, const Source &src, const Map &cm, ui
   return RHJ_OK;
 }
 
+template <class Source, class Map, int TPB>
+static int launch_scatter2(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+                           const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
+                           const uint64_t *bin_base, cudaStream_t st) {
+  size_t smem = scatter2_smem_bytes<Source>(nbins);
+  auto kern = k_scatter2<Source, Map, TPB>;
+  RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem));
+  if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
+  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count * per_sm));
+  kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ctx->tiles_per_chunk, chunk_off, tile_off, tile_start, bin_base, ctx->d_status, ctx->tune_l2_ahead);
+  RHJ_CHECK_LAUNCH("k_scatter2");
+  return RHJ_OK;
+}
+
 template <class Source, class Map>
 static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                          const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st, int ipt) {
+                          const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
+                          const uint64_t *bin_base, cudaStream_t st, int ipt) {
   if (grid_chunks == 0) return RHJ_OK;
-  if (!ctx->tune_legacy_scatter) {
+  if (ctx->tune_scatter == 2) {
+    if (ctx->tune_tpb == 1024)
+      return launch_scatter2<Source, Map, 1024>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
+    return launch_scatter2<Source, Map, 512>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
+  }
+  if (ctx->tune_scatter == 1) {
     // wide fan-outs need the shared memory for the per-bin arrays: fall back to the smaller tile
     if (ipt == 8 && scatter_tma_smem_bytes<Source, 8>(nbins) <= 110 * 1024)
       return launch_scatter_tma<Source, Map, 8>(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
@@ -488,7 +540,8 @@ static int histogram_inputs(rhj_ctx *ctx, cudaStream_t st) {
   for (int k = 0; k < 2; ++k) {
     InputSource<TB> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
     ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
-    int rc = launch_histogram(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], st);
+    int rc = launch_histogram(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k],
+                              ctx->tile1_start[k], st);
     if (rc) return rc;
     dim3 grid((ctx->P + 31) / 32, 1);
     k_colscan<32><<<grid, 32 * 32, 0, st>>>(ctx->chunk1_hist[k], ctx->P, nullptr, ctx->nchunks1[k],
@@ -579,10 +632,10 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
     int rc;
     if (ctx->cfg.tuple_bytes == 16) {
       InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
     } else {
       InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
     }
     if (rc) return rc;
   }
@@ -636,7 +689,8 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
       ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
       ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
                      ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
-      int rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], st);
+      int rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
+                                ctx->tile2_start[k], st);
       if (rc) return rc;
       dim3 grid((L + 31) / 32, ctx->nowned);
       k_colscan<8><<<grid, 8 * 32, 0, st>>>(ctx->chunk2_hist[k], L, ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), 0,
@@ -649,8 +703,8 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
       ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
       ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
                      ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
-      rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k],
-                          ctx->d_sub_addr + (uint64_t)k * ctx->NS, st, ctx->tune_ipt_loc);
+      rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
+                          ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st, ctx->tune_ipt_loc);
       if (rc) return rc;
     }
   }
@@ -666,8 +720,13 @@ static int launch_build_probe(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_
     k_expand_items<CAP><<<(a.NS + 255) / 256, 256, 0, st>>>(a, ctx->d_items);
     RHJ_CHECK_LAUNCH("k_expand_items");
     size_t smem2 = build_probe2_smem_bytes<CAP>();
-    RHJ_CUDA(cudaFuncSetAttribute(k_build_probe2<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-    k_build_probe2<CAP><<<ctx->sm_count, kBp2TPB, smem2, st>>>(a);
+    if (ctx->key_shift == 32) {
+      RHJ_CUDA(cudaFuncSetAttribute(k_build_probe2<CAP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      k_build_probe2<CAP, true><<<ctx->sm_count, kBp2TPB, smem2, st>>>(a);
+    } else {
+      RHJ_CUDA(cudaFuncSetAttribute(k_build_probe2<CAP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      k_build_probe2<CAP, false><<<ctx->sm_count, kBp2TPB, smem2, st>>>(a);
+    }
     RHJ_CHECK_LAUNCH("k_build_probe2");
     return RHJ_OK;
   }

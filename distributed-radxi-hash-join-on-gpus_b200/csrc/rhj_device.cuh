@@ -26,6 +26,8 @@ __device__ __forceinline__ uint64_t ld_stream_u64(const uint64_t *p) {
   asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(r) : "l"(p));
   return r;
 }
+__device__ __forceinline__ ulonglong2 ld_stream(const ulonglong2 *p) { return ld_stream_v2(p); }
+__device__ __forceinline__ uint64_t ld_stream(const uint64_t *p) { return ld_stream_u64(p); }
 // Scatter output is write-once, never re-read by this kernel; may target a peer GPU.
 __device__ __forceinline__ void st_stream_u64(uint64_t *p, uint64_t v) {
   asm volatile("st.global.L1::no_allocate.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -68,14 +70,14 @@ __device__ __forceinline__ uint64_t compress_tuple(uint64_t key, uint64_t rid, u
 }
 
 // Checksum term of one matching pair; bit-identical to oracle/hpcjoin_oracle.c orc_mix().
+// Two 32x32->64 multiply-adds (IMAD.WIDE): the build/probe kernel is issue-bound, so the
+// term is kept to a handful of instructions while still tying key, rid_R and rid_S together.
 __device__ __forceinline__ uint64_t mix_triple(uint64_t key, uint64_t rid_r, uint64_t rid_s) {
-  uint32_t k32 = (uint32_t)key ^ (uint32_t)(key >> 32);
-  uint32_t rr = (uint32_t)rid_r ^ (uint32_t)(rid_r >> 32);
-  uint32_t rs = (uint32_t)rid_s ^ (uint32_t)(rid_s >> 32);
-  uint32_t rot = __funnelshift_l(rs, rs, 16);
-  uint64_t a = (uint64_t)(rr ^ 0x9E3779B9u) * (uint64_t)(rs ^ 0x85EBCA6Bu);
-  uint64_t b = (uint64_t)(k32 ^ 0xC2B2AE35u) * (uint64_t)((rr + rot) ^ 0x27D4EB2Fu);
-  return a ^ b;
+  const uint32_t k32 = (uint32_t)key ^ (uint32_t)(key >> 32);
+  const uint32_t rr = (uint32_t)rid_r ^ (uint32_t)(rid_r >> 32);
+  const uint32_t rs = (uint32_t)rid_s ^ (uint32_t)(rid_s >> 32);
+  const uint64_t a = (uint64_t)(rr ^ 0x9E3779B9u) * (uint64_t)(rs ^ 0x85EBCA6Bu);
+  return a + (uint64_t)(k32 ^ 0xC2B2AE35u) * (uint64_t)(uint32_t)(rr + rs + 0x27D4EB2Fu);
 }
 
 // ---- scans -------------------------------------------------------------------------
@@ -203,4 +205,19 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+}  // namespace rhj
+
+namespace rhj {
+// Ask L2 to fetch a contiguous range ahead of time (no registers, no shared memory, no
+// completion to wait for).  Lets the real loads, issued a tile or two later, hit in the
+// 126 MB L2 instead of paying the loaded HBM latency.  addr 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void prefetch_l2_bulk(const void *addr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(addr), "r"(bytes) : "memory");
+}
+// [p, p+bytes) shrunk to 16-byte boundaries, then prefetched
+__device__ __forceinline__ void prefetch_l2_range(const void *p, uint64_t bytes) {
+  const uintptr_t a0 = (reinterpret_cast<uintptr_t>(p) + 15) & ~uintptr_t(15);
+  const uintptr_t a1 = (reinterpret_cast<uintptr_t>(p) + bytes) & ~uintptr_t(15);
+  if (a1 > a0) prefetch_l2_bulk(reinterpret_cast<const void *>(a0), (uint32_t)(a1 - a0));
+}
 }  // namespace rhj

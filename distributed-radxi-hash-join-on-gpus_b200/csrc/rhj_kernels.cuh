@@ -24,6 +24,7 @@ constexpr int kScatTPB = 512;
 constexpr int kScatIPT = 8;
 constexpr int kScatTile = kScatTPB * kScatIPT;  // tuples staged in shared memory per tile
 constexpr uint32_t kInvalidDigit = 0xFFFFFFFFu;
+constexpr int kScatL2Ahead = 3;  // tiles between the register prefetch and the L2 prefetch
 
 enum DevStatus : int {
   kDevOk = 0,
@@ -163,6 +164,276 @@ __global__ void __launch_bounds__(kHistTPB) k_histogram(Source src, Map cm, uint
       chunk_hist[(uint64_t)c * nbins + i] = s;
     }
     __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// K1t: histogram with tile granularity.  The histogram kernels have instruction and
+// shared-memory slack (they only read), the scatter kernels have none; so everything
+// the scatter would otherwise have to derive per tile is computed here, once:
+//   chunk_hist [chunk][nbins] u32   counts per chunk (as k_histogram)
+//   tile_off   [row][nbins]   u32   tuples of the bin in EARLIER tiles of the same chunk
+//   tile_start [row][nbins]   u16   exclusive prefix over the bins inside the tile
+//                                   (= where the bin's run starts in the sorted tile)
+// row = chunk * tiles_per_chunk + tile; a tile is kScatTile tuples.
+// ---------------------------------------------------------------------------------
+static_assert(kHistTPB * kHistUnroll == kScatTile, "histogram tile must equal the scatter tile");
+
+template <class Source, class Map>
+__global__ void __launch_bounds__(kHistTPB, 4) k_histogram_tiles(Source src, Map cm, uint32_t nbins, uint32_t nrep,
+                                                               uint32_t tiles_per_chunk,
+                                                               uint32_t *__restrict__ chunk_hist,
+                                                               uint32_t *__restrict__ tile_off,
+                                                               uint16_t *__restrict__ tile_start,
+                                                               const int *__restrict__ status) {
+  extern __shared__ uint32_t sh_hist[];  // [2][nrep][nbins] counters | [nbins] running | tmp[2][33]
+  if (*status != kDevOk) return;
+  uint32_t *running = sh_hist + 2 * nrep * nbins;
+  uint32_t *tmp = running + nbins;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t nchunks = cm.count();
+  const bool fast = nbins <= kHistTPB;  // one bin per thread: two barriers per tile, counters double-buffered
+  for (uint32_t i = tid; i < 2 * nbins * nrep; i += kHistTPB) sh_hist[i] = 0;
+  uint32_t par = 0;
+  for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    for (uint32_t i = tid; i < nbins; i += kHistTPB) running[i] = 0;
+    __syncthreads();
+    uint64_t b, e;
+    uint32_t seg;
+    cm.range(c, b, e, seg);
+    uint64_t row = (uint64_t)c * tiles_per_chunk;
+    for (uint64_t base = b; base < e; base += kScatTile, ++row, par ^= 1) {
+      uint32_t *set = sh_hist + par * nrep * nbins;
+      uint32_t *my = set + (warp % nrep) * nbins;
+      uint32_t dg[kHistUnroll];
+#pragma unroll
+      for (int u = 0; u < kHistUnroll; ++u) {
+        uint64_t i = base + (uint64_t)u * kHistTPB + tid;
+        dg[u] = i < e ? src.digit(i) : kInvalidDigit;
+      }
+#pragma unroll
+      for (int u = 0; u < kHistUnroll; ++u)
+        if (dg[u] != kInvalidDigit) atomicAdd(&my[dg[u]], 1u);
+      __syncthreads();
+      if (fast) {
+        uint32_t cnt = 0;
+        if (tid < nbins) {
+          for (uint32_t r = 0; r < nrep; ++r) {
+            cnt += set[r * nbins + tid];
+            set[r * nbins + tid] = 0;
+          }
+        }
+        const uint32_t incl = warp_inclusive_scan(cnt);
+        uint32_t *wt = tmp + par * 33;
+        if (lane == 31) wt[warp] = incl;
+        __syncthreads();
+        if (tid < nbins) {
+          uint32_t before = 0;
+          for (uint32_t w = 0; w < warp; ++w) before += wt[w];
+          const uint32_t run = running[tid];
+          tile_off[row * nbins + tid] = run;
+          tile_start[row * nbins + tid] = (uint16_t)(before + incl - cnt);
+          running[tid] = run + cnt;
+        }
+      } else {
+        uint32_t carry = 0;
+        for (uint32_t d0 = 0; d0 < nbins; d0 += kHistTPB) {
+          const uint32_t d = d0 + tid;
+          uint32_t cnt = 0;
+          if (d < nbins) {
+            for (uint32_t r = 0; r < nrep; ++r) {
+              cnt += set[r * nbins + d];
+              set[r * nbins + d] = 0;
+            }
+          }
+          uint32_t total;
+          const uint32_t ex = block_exclusive_scan<uint32_t>(cnt, tmp, &total);
+          if (d < nbins) {
+            const uint32_t run = running[d];
+            tile_off[row * nbins + d] = run;
+            tile_start[row * nbins + d] = (uint16_t)(carry + ex);
+            running[d] = run + cnt;
+          }
+          carry += total;
+        }
+      }
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < nbins; i += kHistTPB) chunk_hist[(uint64_t)c * nbins + i] = running[i];
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// K2 / K3, offset-driven: every (tile, bin) destination and every bin's position inside
+// the sorted tile is known before the kernel starts (k_histogram_tiles + k_colscan), so
+// a tile needs no counting and no scan here: one shared atomic per tuple hands out its
+// slot in the staging buffer, and one barrier per tile separates "place tile k+1" from
+// "write tile k+1".  The loop is software-pipelined over tiles:
+//     iteration k:  write tile k (staged last iteration)  |  place tile k+1 (loaded last
+//     iteration) | issue loads of tile k+2 | prepare the per-bin slots of tile k+2 | barrier
+// Staging buffers alternate (2), the per-bin slot/address arrays rotate (3), so nothing
+// read in an iteration is written in the same one.
+// ---------------------------------------------------------------------------------
+template <class Source>
+__host__ __device__ inline size_t scatter2_smem_bytes(uint32_t nbins) {
+  return 2 * (size_t)kScatTile * 8 + (Source::kDigitFromValue ? 0 : 2 * (size_t)kScatTile * 2) +
+         3 * (size_t)nbins * (8 + 4) + 64;
+}
+
+template <class Source, class Map, int TPB>
+__global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1)
+    k_scatter2(Source src, Map cm, uint32_t nbins, uint32_t tiles_per_chunk,
+               const uint32_t *__restrict__ chunk_off, const uint32_t *__restrict__ tile_off,
+               const uint16_t *__restrict__ tile_start, const uint64_t *__restrict__ bin_base,
+               const int *__restrict__ status, int l2_ahead) {
+  using Raw = typename Source::Raw;
+  constexpr int IPT = kScatTile / TPB;
+  constexpr uint32_t T = kScatTile;
+  extern __shared__ __align__(128) unsigned char sh_raw[];
+  if (*status != kDevOk) return;
+  uint64_t *stage = reinterpret_cast<uint64_t *>(sh_raw);             // [2][T]
+  uint64_t *delta = stage + 2 * T;                                    // [3][nbins]
+  uint32_t *pos = reinterpret_cast<uint32_t *>(delta + 3 * nbins);    // [3][nbins]
+  uint16_t *dig = reinterpret_cast<uint16_t *>(pos + 3 * nbins);      // [2][T]   (pass 1 only)
+  const uint32_t tid = threadIdx.x;
+  const uint32_t nchunks = cm.count();
+  const Raw *gin = static_cast<const Raw *>(src.base());
+
+  struct Tile {
+    uint64_t t0, e;
+    uint32_t c, t, seg;
+    bool valid;
+  };
+  auto open_chunk = [&](Tile &x, uint32_t c) {
+    x.c = c;
+    x.t = 0;
+    x.valid = c < nchunks;
+    if (x.valid) cm.range(c, x.t0, x.e, x.seg);
+  };
+  auto next_tile = [&](const Tile &x) {
+    Tile y = x;
+    if (!x.valid) return y;
+    y.t0 += T;
+    y.t += 1;
+    if (y.t0 >= y.e) open_chunk(y, x.c + gridDim.x);
+    return y;
+  };
+  auto tile_n = [&](const Tile &x) { return (x.e - x.t0) < (uint64_t)T ? (uint32_t)(x.e - x.t0) : T; };
+
+  // per-bin slot counter and destination of a tile, for bin d (thread d)
+  auto small_load = [&](const Tile &x, uint32_t d, uint32_t &lst, uint64_t &dst) {
+    const uint64_t row = (uint64_t)x.c * tiles_per_chunk + x.t;
+    lst = tile_start[row * nbins + d];
+    const uint32_t off = chunk_off[(uint64_t)x.c * nbins + d] + tile_off[row * nbins + d];
+    dst = bin_base[(uint64_t)x.seg * nbins + d] + ((uint64_t)off - lst) * 8;
+  };
+  auto small_init = [&](const Tile &x, uint32_t buf) {
+    if (!x.valid) return;
+    for (uint32_t d = tid; d < nbins; d += TPB) {
+      uint32_t lst;
+      uint64_t dst;
+      small_load(x, d, lst, dst);
+      pos[buf * nbins + d] = lst;
+      delta[buf * nbins + d] = dst;
+    }
+  };
+  auto load_raw = [&](const Tile &x, Raw (&raw)[IPT]) {
+    if (!x.valid) return;
+    const uint32_t n = tile_n(x);
+#pragma unroll
+    for (int u = 0; u < IPT; ++u) {
+      const uint32_t i = u * TPB + tid;
+      if (i < n) raw[u] = ld_stream(gin + x.t0 + i);
+    }
+  };
+  auto place = [&](const Tile &x, const Raw (&raw)[IPT], uint32_t sb, uint32_t buf) {
+    if (!x.valid) return;
+    const uint32_t n = tile_n(x);
+    uint64_t *st = stage + sb * T;
+    uint16_t *dg_out = dig + sb * T;
+    uint32_t *ps = pos + buf * nbins;
+#pragma unroll
+    for (int u = 0; u < IPT; ++u) {
+      const uint32_t i = u * TPB + tid;
+      if (i < n) {
+        uint64_t v;
+        uint32_t d;
+        src.decode(raw[u], v, d);
+        const uint32_t p = atomicAdd(&ps[d], 1u);
+        st[p] = v;
+        if (!Source::kDigitFromValue) dg_out[p] = (uint16_t)d;
+      }
+    }
+  };
+  auto write_out = [&](const Tile &x, uint32_t sb, uint32_t buf) {
+    const uint32_t n = tile_n(x);
+    const uint64_t *st = stage + sb * T;
+    const uint16_t *dg_in = dig + sb * T;
+    const uint64_t *dl = delta + buf * nbins;
+#pragma unroll
+    for (int u = 0; u < IPT; ++u) {
+      const uint32_t i = u * TPB + tid;
+      if (i < n) {
+        const uint64_t v = st[i];
+        const uint32_t d = Source::kDigitFromValue ? src.digit_of_value(v) : (uint32_t)dg_in[i];
+        st_stream_u64(reinterpret_cast<uint64_t *>(dl[d] + (uint64_t)i * 8), v);
+      }
+    }
+  };
+
+  Tile A, B;
+  open_chunk(A, blockIdx.x);
+  if (!A.valid) return;
+  B = next_tile(A);
+  Raw raw[IPT];
+  small_init(A, 0);
+  load_raw(A, raw);
+  __syncthreads();
+  place(A, raw, 0, 0);
+  small_init(B, 1);
+  load_raw(B, raw);
+  __syncthreads();
+
+  // warp 0 walks a fourth iterator kL2Ahead tiles beyond C and asks L2 for that tile
+  Tile D = B;
+  if (tid < 32) {
+    for (int i = 0; i < l2_ahead; ++i) {
+      D = next_tile(D);
+      if (tid == 0 && D.valid) prefetch_l2_range(gin + D.t0, (uint64_t)tile_n(D) * sizeof(Raw));
+    }
+  }
+  uint32_t sb = 0, buf = 0;  // staging buffer / slot-array set of tile A
+  while (A.valid) {
+    const Tile C = next_tile(B);
+    if (tid < 32 && l2_ahead > 0) {
+      D = next_tile(D);
+      if (tid == 0 && D.valid) prefetch_l2_range(gin + D.t0, (uint64_t)tile_n(D) * sizeof(Raw));
+    }
+    const uint32_t buf1 = buf == 2 ? 0 : buf + 1, buf2 = buf1 == 2 ? 0 : buf1 + 1;
+    // slots of tile k+2: loads now, stores after the work below (one bin per thread in the common case)
+    uint32_t lst = 0;
+    uint64_t dst = 0;
+    const bool small_fast = nbins <= (uint32_t)TPB;
+    if (C.valid && small_fast && tid < nbins) small_load(C, tid, lst, dst);
+    write_out(A, sb, buf);
+    place(B, raw, sb ^ 1, buf1);
+    if (C.valid) {
+      if (small_fast) {
+        if (tid < nbins) {
+          pos[buf2 * nbins + tid] = lst;
+          delta[buf2 * nbins + tid] = dst;
+        }
+      } else {
+        small_init(C, buf2);
+      }
+    }
+    load_raw(C, raw);
+    __syncthreads();
+    A = B;
+    B = C;
+    sb ^= 1;
+    buf = buf1;
   }
 }
 
@@ -358,7 +629,7 @@ __global__ void __launch_bounds__(kScatTPB, 2) k_scatter(Source src, Map cm, uin
                                                           const uint32_t *__restrict__ chunk_off,
                                                           const uint64_t *__restrict__ bin_base,
                                                           const int *__restrict__ status) {
-  extern __shared__ __align__(16) unsigned char sh_raw[];
+  extern __shared__ __align__(128) unsigned char sh_raw[];
   if (*status != kDevOk) return;
   ScatterSmem s;
   s.stage = reinterpret_cast<uint64_t *>(sh_raw);
@@ -773,7 +1044,7 @@ __host__ __device__ constexpr size_t build_probe_smem_bytes() {
 
 template <int CAP>
 __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
-  extern __shared__ __align__(16) unsigned char sh_raw[];
+  extern __shared__ __align__(128) unsigned char sh_raw[];
   __shared__ unsigned long long s_item;
   __shared__ unsigned long long s_red[5][kBpTPB / 32];
   if (*a.status != kDevOk) return;
@@ -915,7 +1186,7 @@ __host__ __device__ constexpr size_t build_probe2_smem_bytes() {
   return (size_t)CAP * (8 + 8 + 4 + 2) + 64;
 }
 
-template <int CAP>
+template <int CAP, bool KS32>
 __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
   extern __shared__ __align__(128) unsigned char sh_raw[];
   __shared__ unsigned long long s_red[5][kBp2TPB / 32];
@@ -926,6 +1197,7 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
   uint64_t *bars = reinterpret_cast<uint64_t *>(next + CAP);
   const uint32_t tid = threadIdx.x;
   const uint64_t rid_mask = a.key_shift >= 64 ? ~0ull : ((1ull << a.key_shift) - 1);
+  const uint32_t hash_shift32 = a.shift_bits - 32;  // KS32: hash bits start inside the high word
   const uint64_t total = a.item_jstart[a.nowned];
   const uint64_t stride = gridDim.x;
 
@@ -995,11 +1267,20 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
     load_batch(sp, head, nv, 0, xs_cur);
   }
 
+  // Sum of keys is folded per item: key = (kpart << F_net) | partition, partition constant per item.
   uint64_t acc_n = 0, acc_key = 0, acc_rr = 0, acc_rs = 0, acc_mix = 0;
   uint32_t s = 0, phase0 = 0, phase1 = 0;
   while (v_cur) {
     v_n2 = id + 2 * stride < total;
     if (v_n2) n2 = fetch(id + 2 * stride);  // needed only at the bottom of the loop
+    // thread 0 also looks one item further and asks L2 for its slices at the bottom of the loop
+    ulonglong2 pf_lo = make_ulonglong2(0, 0), pf_hi = make_ulonglong2(0, 0);
+    const bool pf = tid == 0 && id + 3 * stride < total && id + 3 * stride < a.items_cap;
+    if (pf) {
+      const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(a.items + id + 3 * stride);
+      pf_lo = p[0];
+      pf_hi = p[1];
+    }
     if (v_n1) {
       issue_build(n1, tup[s ^ 1], &bars[s ^ 1]);
       const uint64_t *sp;
@@ -1018,7 +1299,8 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
     // ---- build (BuildProbe.cpp:82-86) ----
     const uint64_t *t = tup[s];
     for (uint32_t i = tid; i < cur.r_n; i += kBp2TPB) {
-      const uint32_t idx = (uint32_t)(t[i] >> a.shift_bits) & hmask;
+      const uint32_t idx = KS32 ? (((uint32_t)(t[i] >> 32) >> hash_shift32) & hmask)
+                                : ((uint32_t)(t[i] >> a.shift_bits) & hmask);
       next[i] = (uint16_t)atomicExch(&bucket[idx], i + 1);
     }
     __syncthreads();
@@ -1026,21 +1308,40 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
     // ---- probe (BuildProbe.cpp:97-106) ----
     {
       const uint32_t partition = cur.partition;
+      uint32_t item_n = 0;
+      uint64_t item_kpart = 0;
       auto probe = [&](uint64_t v) {
-        const uint64_t kpart = v >> a.key_shift;
-        uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
-        while (hit) {
-          const uint64_t r = t[hit - 1];
-          if ((r >> a.key_shift) == kpart) {
-            const uint64_t key = (kpart << a.net_bits) | partition;
-            const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
-            acc_n += 1;
-            acc_key += key;
-            acc_rr += rid_r;
-            acc_rs += rid_s;
-            acc_mix += mix_triple(key, rid_r, rid_s);
+        if (KS32) {  // rid = low word, key part = high word: all comparisons and sums on 32-bit halves
+          const uint32_t vhi = (uint32_t)(v >> 32), vlo = (uint32_t)v;
+          uint32_t hit = bucket[(vhi >> hash_shift32) & hmask];
+          while (hit) {
+            const uint64_t r = t[hit - 1];
+            if ((uint32_t)(r >> 32) == vhi) {
+              const uint32_t rlo = (uint32_t)r;
+              item_n += 1;
+              item_kpart += vhi;
+              acc_rr += rlo;
+              acc_rs += vlo;
+              const uint64_t key = ((uint64_t)vhi << a.net_bits) | partition;
+              acc_mix += mix_triple(key, rlo, vlo);
+            }
+            hit = next[hit - 1];
           }
-          hit = next[hit - 1];
+        } else {
+          const uint64_t kpart = v >> a.key_shift;
+          uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
+          while (hit) {
+            const uint64_t r = t[hit - 1];
+            if ((r >> a.key_shift) == kpart) {
+              const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
+              item_n += 1;
+              item_kpart += kpart;
+              acc_rr += rid_r;
+              acc_rs += rid_s;
+              acc_mix += mix_triple((kpart << a.net_bits) | partition, rid_r, rid_s);
+            }
+            hit = next[hit - 1];
+          }
         }
       };
       const uint64_t *sp;
@@ -1060,6 +1361,13 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
           }
         }
       }
+      acc_n += item_n;
+      acc_key += (item_kpart << a.net_bits) + (uint64_t)item_n * partition;
+    }
+    if (pf) {
+      prefetch_l2_range(a.src[0] + pf_lo.x, (uint64_t)(uint32_t)pf_hi.x * 8);
+      const uint32_t sn = (uint32_t)(pf_hi.x >> 32);
+      prefetch_l2_range(a.src[1] + pf_lo.y, (uint64_t)(sn < (uint32_t)kBp2Batch ? sn : (uint32_t)kBp2Batch) * 8);
     }
     fence_proxy_async_smem();
     __syncthreads();

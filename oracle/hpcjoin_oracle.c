@@ -299,10 +299,9 @@ uint64_t orc_mix(uint64_t key, uint64_t rid_r, uint64_t rid_s) {
   uint32_t k32 = (uint32_t)key ^ (uint32_t)(key >> 32);
   uint32_t rr = (uint32_t)rid_r ^ (uint32_t)(rid_r >> 32);
   uint32_t rs = (uint32_t)rid_s ^ (uint32_t)(rid_s >> 32);
-  uint32_t rot = (rs << 16) | (rs >> 16);
   uint64_t a = (uint64_t)(rr ^ 0x9E3779B9u) * (uint64_t)(rs ^ 0x85EBCA6Bu);
-  uint64_t b = (uint64_t)(k32 ^ 0xC2B2AE35u) * (uint64_t)((rr + rot) ^ 0x27D4EB2Fu);
-  return a ^ b;
+  uint64_t b = (uint64_t)(k32 ^ 0xC2B2AE35u) * (uint64_t)(uint32_t)(rr + rs + 0x27D4EB2Fu);
+  return a + b;
 }
 
 /* tasks/BuildProbe.cpp:16-25 -- 32-bit-safe round-up, kept as is */
