@@ -116,7 +116,7 @@ struct rhj_ctx {
   // tuning knobs (environment: RHJ_SCATTER=legacy, RHJ_IPT_NET, RHJ_IPT_LOC, RHJ_BP=legacy)
   int tune_scatter = 2;  // 0 legacy, 1 TMA-staged input, 2 offset-driven (default)
   bool tune_legacy_bp = false;
-  int tune_ipt_net = 4, tune_ipt_loc = 8, tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4;
+  int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
 };
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
@@ -180,13 +180,12 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
-  if (const char *e = getenv("RHJ_SCATTER")) c->tune_scatter = strcmp(e, "legacy") == 0 ? 0 : strcmp(e, "tma") == 0 ? 1 : 2;
+  if (const char *e = getenv("RHJ_SCATTER")) c->tune_scatter = strcmp(e, "legacy") == 0 ? 0 : 2;
   if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
   if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = std::max(0, std::min(32, atoi(e)));
   if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
   if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
-  if (const char *e = getenv("RHJ_IPT_NET")) c->tune_ipt_net = atoi(e) == 8 ? 8 : 4;
-  if (const char *e = getenv("RHJ_IPT_LOC")) c->tune_ipt_loc = atoi(e) == 8 ? 8 : 4;
+  if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
   *out = c;
   return RHJ_OK;
 }
@@ -273,7 +272,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   auto add = [&](uint64_t bytes) { total += align_up(bytes ? bytes : 1, kAlign); };
   for (int k = 0; k < 2; ++k) {
     lay->window_cap[k] = wcap_in[k] ? wcap_in[k] : default_window_cap(cfg, max_local[k]);
-    lay->localout_tuples[k] = cfg->enable_two_level ? lay->window_cap[k] + NS * 8 : 0;
+    lay->localout_tuples[k] = cfg->enable_two_level ? lay->window_cap[k] + NS * 8 + (uint64_t)nowned * 8 + 16 : 0;
     lay->max_chunks1[k] = (uint32_t)std::max<uint64_t>(1, (max_local[k] + chunk - 1) / chunk);
     lay->max_chunks2[k] = cfg->enable_two_level ? (uint32_t)((lay->window_cap[k] + chunk - 1) / chunk + nowned) : 0;
     add(lay->window_cap[k] * 8);
@@ -480,52 +479,32 @@ static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint
   return RHJ_OK;
 }
 
-template <class Source, class Map, int IPT>
-static int launch_scatter_tma(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                              const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
-  size_t smem = scatter_tma_smem_bytes<Source, IPT>(nbins);
-  auto kern = k_scatter_tma<Source, Map, IPT>;
-  RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScatTPB, smem));
-  if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
-  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count * per_sm));
-  kern<<<grid, kScatTPB, smem, st>>>(src, cm, nbins, chunk_off, bin_base, ctx->d_status);
-  RHJ_CHECK_LAUNCH("k_scatter_tma");
-  return RHJ_OK;
-}
-
 template <class Source, class Map, int TPB>
-static int launch_scatter2(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+static int launch_scatter3(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
                            const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
                            const uint64_t *bin_base, cudaStream_t st) {
-  size_t smem = scatter2_smem_bytes<Source>(nbins);
-  auto kern = k_scatter2<Source, Map, TPB>;
+  size_t smem = scatter3_smem_bytes<Source>(nbins);
+  auto kern = k_scatter3<Source, Map, TPB>;
   RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem));
   if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
   uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count * per_sm));
-  kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ctx->tiles_per_chunk, chunk_off, tile_off, tile_start, bin_base, ctx->d_status, ctx->tune_l2_ahead);
-  RHJ_CHECK_LAUNCH("k_scatter2");
+  kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ctx->tiles_per_chunk, chunk_off, tile_off, tile_start, bin_base,
+                                ctx->d_status, ctx->tune_l2_ahead);
+  RHJ_CHECK_LAUNCH("k_scatter3");
   return RHJ_OK;
 }
 
 template <class Source, class Map>
 static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
                           const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
-                          const uint64_t *bin_base, cudaStream_t st, int ipt) {
+                          const uint64_t *bin_base, cudaStream_t st) {
   if (grid_chunks == 0) return RHJ_OK;
   if (ctx->tune_scatter == 2) {
     if (ctx->tune_tpb == 1024)
-      return launch_scatter2<Source, Map, 1024>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
-    return launch_scatter2<Source, Map, 512>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
-  }
-  if (ctx->tune_scatter == 1) {
-    // wide fan-outs need the shared memory for the per-bin arrays: fall back to the smaller tile
-    if (ipt == 8 && scatter_tma_smem_bytes<Source, 8>(nbins) <= 110 * 1024)
-      return launch_scatter_tma<Source, Map, 8>(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
-    return launch_scatter_tma<Source, Map, 4>(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
+      return launch_scatter3<Source, Map, 1024>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
+    return launch_scatter3<Source, Map, 512>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
   }
   size_t smem = scatter_smem_bytes(nbins);
   RHJ_CUDA(cudaFuncSetAttribute(k_scatter<Source, Map>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -632,10 +611,10 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
     int rc;
     if (ctx->cfg.tuple_bytes == 16) {
       InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
     } else {
       InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, ctx->tune_ipt_net);
+      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
     }
     if (rc) return rc;
   }
@@ -704,7 +683,7 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
       ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
                      ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
       rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
-                          ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st, ctx->tune_ipt_loc);
+                          ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
       if (rc) return rc;
     }
   }
@@ -716,18 +695,33 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
 
 template <int CAP>
 static int launch_build_probe(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_t st) {
-  if (!ctx->tune_legacy_bp) {
+  // the pipelined kernel relies on the 8-tuple alignment/padding of the local pass; single-pass
+  // mode (arbitrary partition offsets) and wide rids use the generic kernel
+  if (!ctx->tune_legacy_bp && ctx->cfg.enable_two_level) {
     k_expand_items<CAP><<<(a.NS + 255) / 256, 256, 0, st>>>(a, ctx->d_items);
     RHJ_CHECK_LAUNCH("k_expand_items");
-    size_t smem2 = build_probe2_smem_bytes<CAP>();
-    if (ctx->key_shift == 32) {
-      RHJ_CUDA(cudaFuncSetAttribute(k_build_probe2<CAP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-      k_build_probe2<CAP, true><<<ctx->sm_count, kBp2TPB, smem2, st>>>(a);
-    } else {
-      RHJ_CUDA(cudaFuncSetAttribute(k_build_probe2<CAP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-      k_build_probe2<CAP, false><<<ctx->sm_count, kBp2TPB, smem2, st>>>(a);
-    }
-    RHJ_CHECK_LAUNCH("k_build_probe2");
+    size_t smem3 = build_probe3_smem_bytes<CAP>();
+    const bool ks32 = ctx->key_shift == 32;
+    auto launch = [&](auto kern, int tpb) -> int {
+      RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+      int per_sm = 0;
+      RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, tpb, smem3));
+      if (per_sm < 1) per_sm = 1;
+      kern<<<ctx->sm_count * per_sm, tpb, smem3, st>>>(a);
+      return RHJ_OK;
+    };
+    int rc;
+    if (ctx->tune_bp_tpb == 512) rc = ks32 ? launch(k_build_probe3<CAP, 512, true>, 512) : launch(k_build_probe3<CAP, 512, false>, 512);
+    else rc = ks32 ? launch(k_build_probe3<CAP, 1024, true>, 1024) : launch(k_build_probe3<CAP, 1024, false>, 1024);
+    if (rc) return rc;
+    RHJ_CHECK_LAUNCH("k_build_probe3");
+    // items beyond the expanded list (extreme skew) are left to the generic kernel below
+    BuildProbeArgs rest = a;
+    rest.item_begin = ctx->items_cap;
+    size_t smem_g = build_probe_smem_bytes<CAP>();
+    RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
+    k_build_probe<CAP><<<ctx->sm_count, kBpTPB, smem_g, st>>>(rest);
+    RHJ_CHECK_LAUNCH("k_build_probe(overflow)");
     return RHJ_OK;
   }
   size_t smem = build_probe_smem_bytes<CAP>();
@@ -853,7 +847,7 @@ extern "C" int rhj_get_partition_dev(rhj_ctx *ctx, int which, uint32_t p, int af
   if (!rc) rc = copy_out(ctx, &cnt, ctx->d_part_cnt + (uint64_t)which * ctx->nowned + j, 8, nullptr);
   if (rc) return rc;
   if (after_local_pass) {
-    *out_dev = ctx->localout[which] + off + (uint64_t)j * ctx->L * 8;
+    *out_dev = ctx->localout[which] + ((off + (uint64_t)j * (ctx->L * 8 + 8) + 7) & ~7ull);
     *out_tuples = cnt + (uint64_t)ctx->L * 8;
   } else {
     *out_dev = ctx->window[which] + off;

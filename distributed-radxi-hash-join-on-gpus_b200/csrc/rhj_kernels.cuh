@@ -263,177 +263,160 @@ __global__ void __launch_bounds__(kHistTPB, 4) k_histogram_tiles(Source src, Map
     __syncthreads();
   }
 }
-
 // ---------------------------------------------------------------------------------
 // K2 / K3, offset-driven: every (tile, bin) destination and every bin's position inside
-// the sorted tile is known before the kernel starts (k_histogram_tiles + k_colscan), so
-// a tile needs no counting and no scan here: one shared atomic per tuple hands out its
-// slot in the staging buffer, and one barrier per tile separates "place tile k+1" from
-// "write tile k+1".  The loop is software-pipelined over tiles:
-//     iteration k:  write tile k (staged last iteration)  |  place tile k+1 (loaded last
-//     iteration) | issue loads of tile k+2 | prepare the per-bin slots of tile k+2 | barrier
+// the sorted tile is known before the kernel starts (k_histogram_tiles + k_colscan), so a
+// tile needs no counting and no scan here: one shared atomic per tuple hands out its slot
+// in the staging buffer, and ONE barrier per tile separates "place tile t+1" from
+// "write tile t+1".  Inside a chunk the loop is software-pipelined over tiles:
+//     iteration t:  write tile t (staged last iteration) | place tile t+1 (loaded last
+//     iteration) | load tile t+2 into registers | prepare the per-bin slots of tile t+2
+//     | ask L2 for tile t+2+ahead | barrier
 // Staging buffers alternate (2), the per-bin slot/address arrays rotate (3), so nothing
-// read in an iteration is written in the same one.
+// read in an iteration is written in the same one.  Everything is addressed relative to
+// the chunk (32-bit indices, row pointers advanced by nbins per tile) to keep the hot
+// loop short: the kernel is bound by instruction issue and shared-memory wavefronts as
+// much as by HBM.
 // ---------------------------------------------------------------------------------
 template <class Source>
-__host__ __device__ inline size_t scatter2_smem_bytes(uint32_t nbins) {
+__host__ __device__ inline size_t scatter3_smem_bytes(uint32_t nbins) {
   return 2 * (size_t)kScatTile * 8 + (Source::kDigitFromValue ? 0 : 2 * (size_t)kScatTile * 2) +
          3 * (size_t)nbins * (8 + 4) + 64;
 }
 
 template <class Source, class Map, int TPB>
-__global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1)
-    k_scatter2(Source src, Map cm, uint32_t nbins, uint32_t tiles_per_chunk,
+__global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
+    k_scatter3(const Source src, const Map cm, const uint32_t nbins, const uint32_t tiles_per_chunk,
                const uint32_t *__restrict__ chunk_off, const uint32_t *__restrict__ tile_off,
                const uint16_t *__restrict__ tile_start, const uint64_t *__restrict__ bin_base,
-               const int *__restrict__ status, int l2_ahead) {
+               const int *__restrict__ status, const int l2_ahead) {
   using Raw = typename Source::Raw;
   constexpr int IPT = kScatTile / TPB;
   constexpr uint32_t T = kScatTile;
   extern __shared__ __align__(128) unsigned char sh_raw[];
   if (*status != kDevOk) return;
-  uint64_t *stage = reinterpret_cast<uint64_t *>(sh_raw);             // [2][T]
-  uint64_t *delta = stage + 2 * T;                                    // [3][nbins]
-  uint32_t *pos = reinterpret_cast<uint32_t *>(delta + 3 * nbins);    // [3][nbins]
-  uint16_t *dig = reinterpret_cast<uint16_t *>(pos + 3 * nbins);      // [2][T]   (pass 1 only)
+  uint64_t *const stage = reinterpret_cast<uint64_t *>(sh_raw);           // [2][T]
+  uint64_t *const delta = stage + 2 * T;                                  // [3][nbins]
+  uint32_t *const pos = reinterpret_cast<uint32_t *>(delta + 3 * nbins);  // [3][nbins]
+  uint16_t *const dig = reinterpret_cast<uint16_t *>(pos + 3 * nbins);    // [2][T]  (pass 1 only)
   const uint32_t tid = threadIdx.x;
   const uint32_t nchunks = cm.count();
-  const Raw *gin = static_cast<const Raw *>(src.base());
+  const bool one_bin_per_thread = nbins <= (uint32_t)TPB;
 
-  struct Tile {
-    uint64_t t0, e;
-    uint32_t c, t, seg;
-    bool valid;
-  };
-  auto open_chunk = [&](Tile &x, uint32_t c) {
-    x.c = c;
-    x.t = 0;
-    x.valid = c < nchunks;
-    if (x.valid) cm.range(c, x.t0, x.e, x.seg);
-  };
-  auto next_tile = [&](const Tile &x) {
-    Tile y = x;
-    if (!x.valid) return y;
-    y.t0 += T;
-    y.t += 1;
-    if (y.t0 >= y.e) open_chunk(y, x.c + gridDim.x);
-    return y;
-  };
-  auto tile_n = [&](const Tile &x) { return (x.e - x.t0) < (uint64_t)T ? (uint32_t)(x.e - x.t0) : T; };
+  for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    uint64_t cb, ce;
+    uint32_t seg;
+    cm.range(c, cb, ce, seg);
+    const uint32_t count = (uint32_t)(ce - cb);
+    const uint32_t ntiles = (count + T - 1) / T;
+    const Raw *const in = static_cast<const Raw *>(src.base()) + cb;
+    const uint32_t *const toff = tile_off + (size_t)c * tiles_per_chunk * nbins;
+    const uint16_t *const tst = tile_start + (size_t)c * tiles_per_chunk * nbins;
+    const uint32_t *const coff = chunk_off + (size_t)c * nbins;
+    const uint64_t *const bb = bin_base + (size_t)seg * nbins;
+    // destination of this chunk's first tuple of bin `tid`
+    uint64_t cbase = 0;
+    if (one_bin_per_thread && tid < nbins) cbase = bb[tid] + (uint64_t)coff[tid] * 8;
 
-  // per-bin slot counter and destination of a tile, for bin d (thread d)
-  auto small_load = [&](const Tile &x, uint32_t d, uint32_t &lst, uint64_t &dst) {
-    const uint64_t row = (uint64_t)x.c * tiles_per_chunk + x.t;
-    lst = tile_start[row * nbins + d];
-    const uint32_t off = chunk_off[(uint64_t)x.c * nbins + d] + tile_off[row * nbins + d];
-    dst = bin_base[(uint64_t)x.seg * nbins + d] + ((uint64_t)off - lst) * 8;
-  };
-  auto small_init = [&](const Tile &x, uint32_t buf) {
-    if (!x.valid) return;
-    for (uint32_t d = tid; d < nbins; d += TPB) {
-      uint32_t lst;
-      uint64_t dst;
-      small_load(x, d, lst, dst);
-      pos[buf * nbins + d] = lst;
-      delta[buf * nbins + d] = dst;
-    }
-  };
-  auto load_raw = [&](const Tile &x, Raw (&raw)[IPT]) {
-    if (!x.valid) return;
-    const uint32_t n = tile_n(x);
-#pragma unroll
-    for (int u = 0; u < IPT; ++u) {
-      const uint32_t i = u * TPB + tid;
-      if (i < n) raw[u] = ld_stream(gin + x.t0 + i);
-    }
-  };
-  auto place = [&](const Tile &x, const Raw (&raw)[IPT], uint32_t sb, uint32_t buf) {
-    if (!x.valid) return;
-    const uint32_t n = tile_n(x);
-    uint64_t *st = stage + sb * T;
-    uint16_t *dg_out = dig + sb * T;
-    uint32_t *ps = pos + buf * nbins;
-#pragma unroll
-    for (int u = 0; u < IPT; ++u) {
-      const uint32_t i = u * TPB + tid;
-      if (i < n) {
-        uint64_t v;
-        uint32_t d;
-        src.decode(raw[u], v, d);
-        const uint32_t p = atomicAdd(&ps[d], 1u);
-        st[p] = v;
-        if (!Source::kDigitFromValue) dg_out[p] = (uint16_t)d;
+    // per-bin slot counter and destination for tile t, into slot-array set `buf`
+    auto small_init = [&](uint32_t t, uint32_t buf) {
+      for (uint32_t d = tid; d < nbins; d += TPB) {
+        const uint32_t lst = tst[(size_t)t * nbins + d];
+        const uint32_t off = toff[(size_t)t * nbins + d];
+        pos[buf * nbins + d] = lst;
+        delta[buf * nbins + d] = bb[d] + ((uint64_t)coff[d] + off - lst) * 8;
       }
-    }
-  };
-  auto write_out = [&](const Tile &x, uint32_t sb, uint32_t buf) {
-    const uint32_t n = tile_n(x);
-    const uint64_t *st = stage + sb * T;
-    const uint16_t *dg_in = dig + sb * T;
-    const uint64_t *dl = delta + buf * nbins;
+    };
+    auto load_raw = [&](uint32_t t, Raw (&raw)[IPT]) {
+      const uint32_t n = count - t * T;
+      const Raw *p = in + t * T + tid;
+      if (n >= T) {
 #pragma unroll
-    for (int u = 0; u < IPT; ++u) {
-      const uint32_t i = u * TPB + tid;
-      if (i < n) {
-        const uint64_t v = st[i];
-        const uint32_t d = Source::kDigitFromValue ? src.digit_of_value(v) : (uint32_t)dg_in[i];
-        st_stream_u64(reinterpret_cast<uint64_t *>(dl[d] + (uint64_t)i * 8), v);
-      }
-    }
-  };
-
-  Tile A, B;
-  open_chunk(A, blockIdx.x);
-  if (!A.valid) return;
-  B = next_tile(A);
-  Raw raw[IPT];
-  small_init(A, 0);
-  load_raw(A, raw);
-  __syncthreads();
-  place(A, raw, 0, 0);
-  small_init(B, 1);
-  load_raw(B, raw);
-  __syncthreads();
-
-  // warp 0 walks a fourth iterator kL2Ahead tiles beyond C and asks L2 for that tile
-  Tile D = B;
-  if (tid < 32) {
-    for (int i = 0; i < l2_ahead; ++i) {
-      D = next_tile(D);
-      if (tid == 0 && D.valid) prefetch_l2_range(gin + D.t0, (uint64_t)tile_n(D) * sizeof(Raw));
-    }
-  }
-  uint32_t sb = 0, buf = 0;  // staging buffer / slot-array set of tile A
-  while (A.valid) {
-    const Tile C = next_tile(B);
-    if (tid < 32 && l2_ahead > 0) {
-      D = next_tile(D);
-      if (tid == 0 && D.valid) prefetch_l2_range(gin + D.t0, (uint64_t)tile_n(D) * sizeof(Raw));
-    }
-    const uint32_t buf1 = buf == 2 ? 0 : buf + 1, buf2 = buf1 == 2 ? 0 : buf1 + 1;
-    // slots of tile k+2: loads now, stores after the work below (one bin per thread in the common case)
-    uint32_t lst = 0;
-    uint64_t dst = 0;
-    const bool small_fast = nbins <= (uint32_t)TPB;
-    if (C.valid && small_fast && tid < nbins) small_load(C, tid, lst, dst);
-    write_out(A, sb, buf);
-    place(B, raw, sb ^ 1, buf1);
-    if (C.valid) {
-      if (small_fast) {
-        if (tid < nbins) {
-          pos[buf2 * nbins + tid] = lst;
-          delta[buf2 * nbins + tid] = dst;
-        }
+        for (int u = 0; u < IPT; ++u) raw[u] = ld_stream(p + u * TPB);
       } else {
-        small_init(C, buf2);
+#pragma unroll
+        for (int u = 0; u < IPT; ++u)
+          if (u * TPB + tid < n) raw[u] = ld_stream(p + u * TPB);
       }
-    }
-    load_raw(C, raw);
+    };
+    auto place = [&](uint32_t t, const Raw (&raw)[IPT], uint32_t sb, uint32_t buf) {
+      const uint32_t n = count - t * T;
+      uint64_t *st = stage + sb * T;
+      uint16_t *dg_out = dig + sb * T;
+      uint32_t *ps = pos + buf * nbins;
+#pragma unroll
+      for (int u = 0; u < IPT; ++u) {
+        if (n >= T || u * TPB + tid < n) {
+          uint64_t v;
+          uint32_t d;
+          src.decode(raw[u], v, d);
+          const uint32_t p = atomicAdd(&ps[d], 1u);
+          st[p] = v;
+          if (!Source::kDigitFromValue) dg_out[p] = (uint16_t)d;
+        }
+      }
+    };
+    auto write_out = [&](uint32_t t, uint32_t sb, uint32_t buf) {
+      const uint32_t n = count - t * T;
+      const uint64_t *st = stage + sb * T + tid;
+      const uint16_t *dg_in = dig + sb * T + tid;
+      const uint64_t *dl = delta + buf * nbins;
+      const uint32_t byte0 = tid * 8;
+#pragma unroll
+      for (int u = 0; u < IPT; ++u) {
+        if (n >= T || u * TPB + tid < n) {
+          const uint64_t v = st[u * TPB];
+          const uint32_t d = Source::kDigitFromValue ? src.digit_of_value(v) : (uint32_t)dg_in[u * TPB];
+          st_stream_u64(reinterpret_cast<uint64_t *>(dl[d] + (byte0 + u * TPB * 8)), v);
+        }
+      }
+    };
+
+    Raw raw[IPT];
+    small_init(0, 0);
+    load_raw(0, raw);
     __syncthreads();
-    A = B;
-    B = C;
-    sb ^= 1;
-    buf = buf1;
+    place(0, raw, 0, 0);
+    if (ntiles > 1) {
+      small_init(1, 1);
+      load_raw(1, raw);
+    }
+    if (tid == 0)
+      for (int a = 2; a < 2 + l2_ahead && (uint32_t)a < ntiles; ++a)
+        prefetch_l2_range(in + (size_t)a * T, (uint64_t)min(T, count - a * T) * sizeof(Raw));
+    __syncthreads();
+
+    uint32_t sb = 0, buf = 0;
+    for (uint32_t t = 0; t < ntiles; ++t) {
+      const uint32_t buf1 = buf == 2 ? 0 : buf + 1, buf2 = buf1 == 2 ? 0 : buf1 + 1;
+      const bool have2 = t + 2 < ntiles;
+      // slots of tile t+2: loads now, stores after the work below
+      uint32_t lst = 0, off = 0;
+      if (have2 && one_bin_per_thread && tid < nbins) {
+        lst = tst[(size_t)(t + 2) * nbins + tid];
+        off = toff[(size_t)(t + 2) * nbins + tid];
+      }
+      if (tid == 0 && l2_ahead > 0 && t + 2 + l2_ahead < ntiles) {
+        const uint32_t a = t + 2 + l2_ahead;
+        prefetch_l2_range(in + (size_t)a * T, (uint64_t)min(T, count - a * T) * sizeof(Raw));
+      }
+      write_out(t, sb, buf);
+      if (t + 1 < ntiles) place(t + 1, raw, sb ^ 1, buf1);
+      if (have2) {
+        if (one_bin_per_thread) {
+          if (tid < nbins) {
+            pos[buf2 * nbins + tid] = lst;
+            delta[buf2 * nbins + tid] = cbase + ((uint64_t)off - lst) * 8;
+          }
+        } else {
+          small_init(t + 2, buf2);
+        }
+        load_raw(t + 2, raw);
+      }
+      __syncthreads();
+      sb ^= 1;
+      buf = buf1;
+    }
   }
 }
 
@@ -704,180 +687,12 @@ __global__ void __launch_bounds__(kScatTPB, 2) k_scatter(Source src, Map cm, uin
     }
   }
 }
-
-// ---------------------------------------------------------------------------------
-// K2 / K3, pipelined: same tile algorithm as k_scatter, but the input tile is brought
-// into shared memory by a bulk asynchronous copy (TMA, cp.async.bulk -> UBLKCP) that
-// completes on an mbarrier.  Two input stages: while tile k is ranked / placed /
-// written, the copy of tile k+1 is in flight, and as soon as tile k is written out its
-// stage is refilled with tile k+2 -- global-load latency never sits on the critical
-// path and no registers are held across it.  The stage that held tile k's input is
-// reused as its output staging buffer (8 bytes per tuple <= the input it replaces).
-// ---------------------------------------------------------------------------------
-template <class Source, int IPT>
-__host__ __device__ inline size_t scatter_tma_smem_bytes(uint32_t nbins) {
-  constexpr size_t T = (size_t)kScatTPB * IPT;
-  constexpr size_t stage = T * sizeof(typename Source::Raw) + 16;  // +16: a misaligned first element
-  return 2 * stage + (size_t)nbins * (8 + 8 + 4 + 4) + 64 * 4 + (Source::kDigitFromValue ? 0 : T * 2) + 2 * 8 + 128;
-}
-
-template <class Source, class Map, int IPT>
-__global__ void __launch_bounds__(kScatTPB, (IPT <= 4 ? 3 : 2))
-    k_scatter_tma(Source src, Map cm, uint32_t nbins, const uint32_t *__restrict__ chunk_off,
-                  const uint64_t *__restrict__ bin_base, const int *__restrict__ status) {
-  using Raw = typename Source::Raw;
-  constexpr uint32_t T = kScatTPB * IPT;
-  constexpr uint32_t RAWB = sizeof(Raw);
-  constexpr uint32_t STAGE_BYTES = T * RAWB + 16;
-  extern __shared__ __align__(128) unsigned char sh_raw[];
-  if (*status != kDevOk) return;
-  unsigned char *in_stage[2] = {sh_raw, sh_raw + STAGE_BYTES};
-  uint64_t *delta = reinterpret_cast<uint64_t *>(sh_raw + 2 * STAGE_BYTES);
-  uint64_t *cursor = delta + nbins;
-  uint64_t *bars = cursor + nbins;  // [2]
-  uint32_t *cnt = reinterpret_cast<uint32_t *>(bars + 2);
-  uint32_t *start = cnt + nbins;
-  uint32_t *tmp = start + nbins;
-  uint16_t *dig = reinterpret_cast<uint16_t *>(tmp + 64);
-
-  const uint32_t tid = threadIdx.x;
-  const uint32_t nchunks = cm.count();
-  const unsigned char *gbase = static_cast<const unsigned char *>(src.base());
-
-  struct TileIt {
-    uint32_t c, seg;
-    uint64_t e, t0;
-    bool valid;
-  };
-  auto open_chunk = [&](TileIt &it, uint32_t c) {
-    it.c = c;
-    it.valid = c < nchunks;
-    if (it.valid) {
-      uint64_t b;
-      cm.range(c, b, it.e, it.seg);
-      it.t0 = b;
-    }
-  };
-  auto advance = [&](TileIt &it) {
-    if (!it.valid) return;
-    it.t0 += T;
-    if (it.t0 >= it.e) open_chunk(it, it.c + gridDim.x);
-  };
-  // thread 0: start the bulk copy of the tile `it` points at into stage s
-  auto issue = [&](const TileIt &it, uint32_t s) {
-    const uint64_t n = (it.e - it.t0) < (uint64_t)T ? (it.e - it.t0) : (uint64_t)T;
-    const uintptr_t a = reinterpret_cast<uintptr_t>(gbase) + it.t0 * RAWB;
-    const uintptr_t a0 = a & ~uintptr_t(15), a1 = (a + n * RAWB) & ~uintptr_t(15);
-    if (a1 > a0) {
-      mbar_arrive_expect_tx(&bars[s], (uint32_t)(a1 - a0));
-      bulk_g2s(in_stage[s], reinterpret_cast<const void *>(a0), (uint32_t)(a1 - a0), &bars[s]);
-    } else {
-      mbar_arrive(&bars[s]);
-    }
-  };
-
-  if (tid == 0) {
-    mbar_init(&bars[0], 1);
-    mbar_init(&bars[1], 1);
-    mbar_fence_init();
-  }
-  for (uint32_t d = tid; d < nbins; d += kScatTPB) cnt[d] = 0;
-  __syncthreads();
-
-  TileIt cur, nxt;
-  open_chunk(cur, blockIdx.x);
-  nxt = cur;
-  if (cur.valid && tid == 0) issue(cur, 0);
-  advance(nxt);
-  if (nxt.valid && tid == 0) issue(nxt, 1);
-
-  uint32_t s = 0, phase0 = 0, phase1 = 0, cur_chunk = 0xFFFFFFFFu;
-  while (cur.valid) {
-    if (cur.c != cur_chunk) {  // first tile of a chunk: this chunk's write cursors
-      cur_chunk = cur.c;
-      for (uint32_t d = tid; d < nbins; d += kScatTPB)
-        cursor[d] = bin_base[(uint64_t)cur.seg * nbins + d] + (uint64_t)chunk_off[(uint64_t)cur.c * nbins + d] * 8;
-      __syncthreads();
-    }
-    const uint32_t tile_n = (cur.e - cur.t0) < (uint64_t)T ? (uint32_t)(cur.e - cur.t0) : T;
-    const uintptr_t a = reinterpret_cast<uintptr_t>(gbase) + cur.t0 * RAWB;
-    const uint32_t skip = (uint32_t)(a & 15);                       // bytes copied in front of element 0
-    const bool tail_direct = ((a + (uint64_t)tile_n * RAWB) & 15) != 0;  // last element is not in the copy
-    const unsigned char *in = in_stage[s] + skip;
-
-    mbar_wait(&bars[s], s ? phase1 : phase0);
-    if (s) phase1 ^= 1; else phase0 ^= 1;
-
-    uint64_t val[IPT];
-    uint32_t dg[IPT], rk[IPT];
-#pragma unroll
-    for (int u = 0; u < IPT; ++u) {
-      const uint32_t i = u * kScatTPB + tid;
-      dg[u] = kInvalidDigit;
-      if (i < tile_n) {
-        Raw r;
-        if (tail_direct && i == tile_n - 1) r = *reinterpret_cast<const Raw *>(a + (uint64_t)i * RAWB);
-        else r = *reinterpret_cast<const Raw *>(in + (size_t)i * RAWB);
-        src.decode(r, val[u], dg[u]);
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < IPT; ++u)
-      if (dg[u] != kInvalidDigit) rk[u] = atomicAdd(&cnt[dg[u]], 1u);
-    __syncthreads();  // every thread has its input in registers: the stage may be overwritten
-
-    uint32_t carry = 0;
-    for (uint32_t d0 = 0; d0 < nbins; d0 += kScatTPB) {
-      const uint32_t d = d0 + tid;
-      const uint32_t v = d < nbins ? cnt[d] : 0;
-      uint32_t total;
-      const uint32_t ex = block_exclusive_scan<uint32_t>(v, tmp, &total);
-      if (d < nbins) {
-        const uint32_t st = carry + ex;
-        const uint64_t cu = cursor[d];
-        start[d] = st;
-        delta[d] = cu - (uint64_t)st * 8;
-        cursor[d] = cu + (uint64_t)v * 8;
-        cnt[d] = 0;
-      }
-      carry += total;
-    }
-    __syncthreads();
-
-    uint64_t *stage = reinterpret_cast<uint64_t *>(in_stage[s]);
-#pragma unroll
-    for (int u = 0; u < IPT; ++u) {
-      if (dg[u] != kInvalidDigit) {
-        const uint32_t pos = start[dg[u]] + rk[u];
-        stage[pos] = val[u];
-        if (!Source::kDigitFromValue) dig[pos] = (uint16_t)dg[u];
-      }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int u = 0; u < IPT; ++u) {
-      const uint32_t i = u * kScatTPB + tid;
-      if (i < tile_n) {
-        const uint64_t v = stage[i];
-        const uint32_t d = Source::kDigitFromValue ? src.digit_of_value(v) : (uint32_t)dig[i];
-        st_stream_u64(reinterpret_cast<uint64_t *>(delta[d] + (uint64_t)i * 8), v);
-      }
-    }
-    fence_proxy_async_smem();  // generic accesses to this stage happen-before the next bulk copy into it
-    __syncthreads();
-
-    advance(nxt);
-    if (nxt.valid && tid == 0) issue(nxt, s);
-    advance(cur);
-    s ^= 1;
-  }
-}
-
 // ---------------------------------------------------------------------------------
 // Kq: after the local-pass histogram.  One block per owned partition j:
 //   sub_cnt[k][j][l]  (from k_colscan totals)  ->  LocalPartitioning.cpp:165-192:
 //   prefix[l] = sum_{l'<l} roundup8(cnt[l']);  output region of partition j starts at
-//   part_off[j] + j*L*8 (each partition gets its size + L*8 slots, :79-81).
+//   roundup8(part_off[j] + j*(L*8+8)): each partition gets its size + L*8 slots (:79-81) and
+//   starts on an 8-tuple (64-byte) boundary like the reference's pool allocation.
 // Also emits the build/probe work list: a sub-partition pair with both sides
 // non-empty (:116-124) becomes ceil(|R|/cap) * ceil(|S|/sslice) items.
 // With two_level off the "sub-partitions" are the network partitions (L == 1).
@@ -916,7 +731,7 @@ __global__ void __launch_bounds__(256) k_plan_local(PlanLocalArgs a) {
       if (l < L) {
         uint64_t idx = (uint64_t)k * NS + (uint64_t)j * L + l;
         uint64_t prefix = pcarry[k] + ex;
-        uint64_t off = a.two_level ? a.part_off[k * a.nowned + j] + (uint64_t)j * L * 8 + prefix
+        uint64_t off = a.two_level ? round_up8(a.part_off[k * a.nowned + j] + (uint64_t)j * (L * 8 + 8)) + prefix
                                    : a.part_off[k * a.nowned + j];
         a.sub_prefix[idx] = prefix;
         a.sub_off[idx] = off;
@@ -982,6 +797,7 @@ struct BuildProbeArgs {
   const int *status;
   const struct ItemDesc *items;  // [items_cap] expanded work list (k_expand_items)
   uint64_t items_cap;
+  uint64_t item_begin;  // generic kernel: first item it is responsible for
 };
 
 // One build/probe work item, fully resolved: what a CTA needs to start its loads.
@@ -1056,7 +872,7 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
   const uint64_t total_items = a.item_jstart[a.nowned];
 
   uint64_t acc_n = 0, acc_key = 0, acc_rr = 0, acc_rs = 0, acc_mix = 0;
-  uint64_t item = blockIdx.x;
+  uint64_t item = a.item_begin + blockIdx.x;
   while (item < total_items) {
     // decode item -> (j, l, build slice, probe slice)
     const uint32_t j = warp_upper_bound(a.item_jstart, a.nowned, item);
@@ -1148,7 +964,7 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
       if (((s_n - h) & 1) && tid == 0) probe(ld_stream_u64(sp_ptr + s_n - 1));
     }
     // next item (the barrier also protects the table against the next build)
-    if (tid == 0) s_item = atomicAdd(a.work_counter, 1ull) + gridDim.x;
+    if (tid == 0) s_item = a.item_begin + atomicAdd(a.work_counter, 1ull) + gridDim.x;
     __syncthreads();
     item = s_item;
     __syncthreads();
@@ -1168,83 +984,38 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
     if (s) atomicAdd(&a.result[tid], s);
   }
 }
-
 // ---------------------------------------------------------------------------------
-// K4, pipelined.  One CTA of 1024 threads per SM, items assigned round-robin.  The
-// loads of item i+1 are started before item i is processed: its build slice by one bulk
-// asynchronous copy (TMA) straight into the second table buffer, the first 4096 probe
-// tuples into registers; its descriptor was fetched one item earlier still.  Build and
-// probe of item i therefore run entirely out of shared memory / registers while the
-// memory system streams the next item.
+// K4, pipelined (two-level mode: sub-partitions start on 8-tuple boundaries and are
+// padded to them, LocalPartitioning.cpp:165-192, so slices are 16-byte aligned and may be
+// over-read up to the padding).  Items are assigned to CTAs round-robin from the expanded
+// work list.  While item i is built and probed out of shared memory / registers, the
+// loads of item i+1 are already in flight: its build slice by one bulk asynchronous copy
+// (TMA) straight into the other table buffer, its first probe batch into registers; the
+// descriptor of item i+2 is fetched at the same time.  Straight-line code per item is
+// kept minimal -- the kernel is bound by instruction issue, not by HBM.
 // ---------------------------------------------------------------------------------
-constexpr int kBp2TPB = 1024;
-constexpr int kBp2SV = 2;                          // 16-byte probe vectors per thread per batch
-constexpr int kBp2Batch = kBp2TPB * kBp2SV * 2;    // probe tuples per batch
+constexpr int kBp3SV = 2;  // 16-byte probe vectors per thread per batch
 
 template <int CAP>
-__host__ __device__ constexpr size_t build_probe2_smem_bytes() {
+__host__ __device__ constexpr size_t build_probe3_smem_bytes() {
   return (size_t)CAP * (8 + 8 + 4 + 2) + 64;
 }
 
-template <int CAP, bool KS32>
-__global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
+template <int CAP, int TPB, bool KS32>
+__global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(const BuildProbeArgs a) {
+  constexpr int BATCH = TPB * kBp3SV * 2;  // probe tuples per batch
   extern __shared__ __align__(128) unsigned char sh_raw[];
-  __shared__ unsigned long long s_red[5][kBp2TPB / 32];
+  __shared__ unsigned long long s_red[5][TPB / 32];
   if (*a.status != kDevOk) return;
-  uint64_t *tup[2] = {reinterpret_cast<uint64_t *>(sh_raw), reinterpret_cast<uint64_t *>(sh_raw) + CAP};
-  uint32_t *bucket = reinterpret_cast<uint32_t *>(tup[1] + CAP);
-  uint16_t *next = reinterpret_cast<uint16_t *>(bucket + CAP);
-  uint64_t *bars = reinterpret_cast<uint64_t *>(next + CAP);
+  uint64_t *const tup0 = reinterpret_cast<uint64_t *>(sh_raw);
+  uint32_t *const bucket = reinterpret_cast<uint32_t *>(tup0 + 2 * CAP);
+  uint16_t *const next = reinterpret_cast<uint16_t *>(bucket + CAP);
+  uint64_t *const bars = reinterpret_cast<uint64_t *>(next + CAP);
   const uint32_t tid = threadIdx.x;
   const uint64_t rid_mask = a.key_shift >= 64 ? ~0ull : ((1ull << a.key_shift) - 1);
   const uint32_t hash_shift32 = a.shift_bits - 32;  // KS32: hash bits start inside the high word
-  const uint64_t total = a.item_jstart[a.nowned];
-  const uint64_t stride = gridDim.x;
-
-  auto fetch = [&](uint64_t item) -> ItemDesc {
-    if (item < a.items_cap) {
-      const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(a.items + item);
-      ulonglong2 lo = p[0], hi = p[1];
-      ItemDesc d;
-      d.r_off = lo.x;
-      d.s_off = lo.y;
-      d.r_n = (uint32_t)hi.x;
-      d.s_n = (uint32_t)(hi.x >> 32);
-      d.partition = (uint32_t)hi.y;
-      d.pad = 0;
-      return d;
-    }
-    return resolve_item<CAP>(a, item, [](const uint64_t *arr, uint32_t n, uint64_t x) { return warp_upper_bound(arr, n, x); });
-  };
-  // start the loads of an item's build slice into table buffer `t`
-  auto issue_build = [&](const ItemDesc &d, uint64_t *t, uint64_t *bar) {
-    const uint64_t *rp = a.src[0] + d.r_off;
-    const uint32_t nbulk = (reinterpret_cast<uintptr_t>(rp) & 15) == 0 ? (d.r_n & ~1u) : 0u;
-    if (tid == 0) {
-      if (nbulk) {
-        mbar_arrive_expect_tx(bar, nbulk * 8);
-        bulk_g2s(t, rp, nbulk * 8, bar);
-      } else {
-        mbar_arrive(bar);
-      }
-    }
-    for (uint32_t i = nbulk + tid; i < d.r_n; i += kBp2TPB) t[i] = ld_stream_u64(rp + i);  // odd tail / unaligned slice
-  };
-  // probe-side addressing: [head scalar][nv 16-byte vectors][tail scalar]
-  auto probe_shape = [&](const ItemDesc &d, const uint64_t *&sp, uint32_t &head, uint32_t &nv) {
-    sp = a.src[1] + d.s_off;
-    head = (reinterpret_cast<uintptr_t>(sp) & 8) ? 1u : 0u;
-    if (head > d.s_n) head = d.s_n;
-    nv = (d.s_n - head) >> 1;
-  };
-  auto load_batch = [&](const uint64_t *sp, uint32_t head, uint32_t nv, uint32_t batch, ulonglong2 (&x)[kBp2SV]) {
-    const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(sp + head);
-#pragma unroll
-    for (int u = 0; u < kBp2SV; ++u) {
-      const uint32_t i = batch * (kBp2TPB * kBp2SV) + u * kBp2TPB + tid;
-      if (i < nv) x[u] = ld_stream_v2(v2 + i);
-    }
-  };
+  const uint64_t total = a.item_jstart[a.nowned] < a.items_cap ? a.item_jstart[a.nowned] : a.items_cap;
+  const uint32_t stride = gridDim.x;
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
@@ -1253,52 +1024,54 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
   }
   __syncthreads();
 
-  uint64_t id = blockIdx.x;
-  bool v_cur = id < total, v_n1 = id + stride < total, v_n2 = false;
-  ItemDesc cur{}, n1{}, n2{};
-  ulonglong2 xs_cur[kBp2SV], xs_n1[kBp2SV];
-  if (v_cur) cur = fetch(id);
-  if (v_n1) n1 = fetch(id + stride);
-  if (v_cur) {
-    issue_build(cur, tup[0], &bars[0]);
-    const uint64_t *sp;
-    uint32_t head, nv;
-    probe_shape(cur, sp, head, nv);
-    load_batch(sp, head, nv, 0, xs_cur);
-  }
+  // descriptor = two 16-byte words {r_off, s_off}, {r_n | s_n << 32, partition}
+  auto fetch = [&](uint64_t item, ulonglong2 &lo, ulonglong2 &hi) {
+    const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(a.items + item);
+    lo = p[0];
+    hi = p[1];
+  };
+  auto issue = [&](const ulonglong2 &lo, const ulonglong2 &hi, uint32_t slot, ulonglong2 (&xs)[kBp3SV]) {
+    const uint32_t r_n = (uint32_t)hi.x, s_n = (uint32_t)(hi.x >> 32);
+    if (tid == 0) {
+      const uint32_t bytes = ((r_n + 1) & ~1u) * 8;  // padded slice: even tuple count
+      mbar_arrive_expect_tx(&bars[slot], bytes);
+      bulk_g2s(tup0 + slot * CAP, a.src[0] + lo.x, bytes, &bars[slot]);
+    }
+    const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(a.src[1] + lo.y) + tid;
+#pragma unroll
+    for (int u = 0; u < kBp3SV; ++u)
+      if (2 * (u * TPB + tid) < s_n) xs[u] = ld_stream_v2(v2 + u * TPB);
+  };
 
-  // Sum of keys is folded per item: key = (kpart << F_net) | partition, partition constant per item.
+  uint64_t id = blockIdx.x;
+  ulonglong2 c_lo, c_hi, n_lo, n_hi;
+  ulonglong2 xs_cur[kBp3SV], xs_nxt[kBp3SV];
+  bool v_cur = id < total, v_nxt = id + stride < total;
+  if (v_cur) {
+    fetch(id, c_lo, c_hi);
+    issue(c_lo, c_hi, 0, xs_cur);
+  }
+  if (v_nxt) fetch(id + stride, n_lo, n_hi);
+
   uint64_t acc_n = 0, acc_key = 0, acc_rr = 0, acc_rs = 0, acc_mix = 0;
-  uint32_t s = 0, phase0 = 0, phase1 = 0;
+  uint32_t slot = 0, phase = 0;  // bit s of `phase` = parity to wait for on bars[s]
   while (v_cur) {
-    v_n2 = id + 2 * stride < total;
-    if (v_n2) n2 = fetch(id + 2 * stride);  // needed only at the bottom of the loop
-    // thread 0 also looks one item further and asks L2 for its slices at the bottom of the loop
-    ulonglong2 pf_lo = make_ulonglong2(0, 0), pf_hi = make_ulonglong2(0, 0);
-    const bool pf = tid == 0 && id + 3 * stride < total && id + 3 * stride < a.items_cap;
-    if (pf) {
-      const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(a.items + id + 3 * stride);
-      pf_lo = p[0];
-      pf_hi = p[1];
-    }
-    if (v_n1) {
-      issue_build(n1, tup[s ^ 1], &bars[s ^ 1]);
-      const uint64_t *sp;
-      uint32_t head, nv;
-      probe_shape(n1, sp, head, nv);
-      load_batch(sp, head, nv, 0, xs_n1);
-    }
-    uint32_t nb = 1;
-    while (nb < cur.r_n) nb <<= 1;
+    ulonglong2 f_lo, f_hi;
+    const bool v_far = id + 2 * (uint64_t)stride < total;
+    if (v_far) fetch(id + 2 * (uint64_t)stride, f_lo, f_hi);
+    if (v_nxt) issue(n_lo, n_hi, slot ^ 1, xs_nxt);
+
+    const uint32_t r_n = (uint32_t)c_hi.x, s_n = (uint32_t)(c_hi.x >> 32), partition = (uint32_t)c_hi.y;
+    const uint32_t nb = r_n <= 1 ? 1u : (1u << (32 - __clz(r_n - 1)));
     const uint32_t hmask = nb - 1;
-    for (uint32_t i = tid; i < nb; i += kBp2TPB) bucket[i] = 0;
+    for (uint32_t i = tid; i < nb; i += TPB) bucket[i] = 0;
     __syncthreads();
-    mbar_wait(&bars[s], s ? phase1 : phase0);
-    if (s) phase1 ^= 1; else phase0 ^= 1;
+    mbar_wait(&bars[slot], (phase >> slot) & 1);
+    phase ^= 1u << slot;
 
     // ---- build (BuildProbe.cpp:82-86) ----
-    const uint64_t *t = tup[s];
-    for (uint32_t i = tid; i < cur.r_n; i += kBp2TPB) {
+    const uint64_t *const t = tup0 + slot * CAP;
+    for (uint32_t i = tid; i < r_n; i += TPB) {
       const uint32_t idx = KS32 ? (((uint32_t)(t[i] >> 32) >> hash_shift32) & hmask)
                                 : ((uint32_t)(t[i] >> a.shift_bits) & hmask);
       next[i] = (uint16_t)atomicExch(&bucket[idx], i + 1);
@@ -1306,79 +1079,72 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
     __syncthreads();
 
     // ---- probe (BuildProbe.cpp:97-106) ----
-    {
-      const uint32_t partition = cur.partition;
-      uint32_t item_n = 0;
-      uint64_t item_kpart = 0;
-      auto probe = [&](uint64_t v) {
-        if (KS32) {  // rid = low word, key part = high word: all comparisons and sums on 32-bit halves
-          const uint32_t vhi = (uint32_t)(v >> 32), vlo = (uint32_t)v;
-          uint32_t hit = bucket[(vhi >> hash_shift32) & hmask];
-          while (hit) {
-            const uint64_t r = t[hit - 1];
-            if ((uint32_t)(r >> 32) == vhi) {
-              const uint32_t rlo = (uint32_t)r;
-              item_n += 1;
-              item_kpart += vhi;
-              acc_rr += rlo;
-              acc_rs += vlo;
-              const uint64_t key = ((uint64_t)vhi << a.net_bits) | partition;
-              acc_mix += mix_triple(key, rlo, vlo);
-            }
-            hit = next[hit - 1];
+    uint32_t item_n = 0;
+    uint64_t item_kpart = 0;
+    auto probe = [&](uint64_t v) {
+      if (KS32) {  // rid = low word, key part = high word
+        const uint32_t vhi = (uint32_t)(v >> 32), vlo = (uint32_t)v;
+        uint32_t hit = bucket[(vhi >> hash_shift32) & hmask];
+        while (hit) {
+          const uint64_t r = t[hit - 1];
+          if ((uint32_t)(r >> 32) == vhi) {
+            const uint32_t rlo = (uint32_t)r;
+            item_n += 1;
+            item_kpart += vhi;
+            acc_rr += rlo;
+            acc_rs += vlo;
+            acc_mix += mix_triple(((uint64_t)vhi << a.net_bits) | partition, rlo, vlo);
           }
-        } else {
-          const uint64_t kpart = v >> a.key_shift;
-          uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
-          while (hit) {
-            const uint64_t r = t[hit - 1];
-            if ((r >> a.key_shift) == kpart) {
-              const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
-              item_n += 1;
-              item_kpart += kpart;
-              acc_rr += rid_r;
-              acc_rs += rid_s;
-              acc_mix += mix_triple((kpart << a.net_bits) | partition, rid_r, rid_s);
-            }
-            hit = next[hit - 1];
-          }
+          hit = next[hit - 1];
         }
-      };
-      const uint64_t *sp;
-      uint32_t head, nv;
-      probe_shape(cur, sp, head, nv);
-      if (tid == 0 && head) probe(ld_stream_u64(sp));
-      if (tid == 1 && ((cur.s_n - head) & 1)) probe(ld_stream_u64(sp + cur.s_n - 1));
-      const uint32_t nbatch = (nv + kBp2TPB * kBp2SV - 1) / (kBp2TPB * kBp2SV);
-      for (uint32_t b = 0; b < nbatch; ++b) {
-        if (b > 0) load_batch(sp, head, nv, b, xs_cur);
-#pragma unroll
-        for (int u = 0; u < kBp2SV; ++u) {
-          const uint32_t i = b * (kBp2TPB * kBp2SV) + u * kBp2TPB + tid;
-          if (i < nv) {
-            probe(xs_cur[u].x);
-            probe(xs_cur[u].y);
+      } else {
+        const uint64_t kpart = v >> a.key_shift;
+        uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
+        while (hit) {
+          const uint64_t r = t[hit - 1];
+          if ((r >> a.key_shift) == kpart) {
+            const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
+            item_n += 1;
+            item_kpart += kpart;
+            acc_rr += rid_r;
+            acc_rs += rid_s;
+            acc_mix += mix_triple((kpart << a.net_bits) | partition, rid_r, rid_s);
           }
+          hit = next[hit - 1];
         }
       }
-      acc_n += item_n;
-      acc_key += (item_kpart << a.net_bits) + (uint64_t)item_n * partition;
+    };
+    {
+      const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(a.src[1] + c_lo.y) + tid;
+      for (uint32_t base = 0; base < s_n; base += BATCH) {
+        if (base > 0) {
+#pragma unroll
+          for (int u = 0; u < kBp3SV; ++u)
+            if (base + 2 * (u * TPB + tid) < s_n) xs_cur[u] = ld_stream_v2(v2 + base / 2 + u * TPB);
+        }
+#pragma unroll
+        for (int u = 0; u < kBp3SV; ++u) {
+          const uint32_t e = base + 2 * (u * TPB + tid);
+          if (e < s_n) probe(xs_cur[u].x);
+          if (e + 1 < s_n) probe(xs_cur[u].y);
+        }
+      }
     }
-    if (pf) {
-      prefetch_l2_range(a.src[0] + pf_lo.x, (uint64_t)(uint32_t)pf_hi.x * 8);
-      const uint32_t sn = (uint32_t)(pf_hi.x >> 32);
-      prefetch_l2_range(a.src[1] + pf_lo.y, (uint64_t)(sn < (uint32_t)kBp2Batch ? sn : (uint32_t)kBp2Batch) * 8);
-    }
+    acc_n += item_n;
+    acc_key += (item_kpart << a.net_bits) + (uint64_t)item_n * partition;
+
     fence_proxy_async_smem();
     __syncthreads();
-    cur = n1;
+    c_lo = n_lo;
+    c_hi = n_hi;
 #pragma unroll
-    for (int u = 0; u < kBp2SV; ++u) xs_cur[u] = xs_n1[u];
-    v_cur = v_n1;
-    n1 = n2;
-    v_n1 = v_n2;
+    for (int u = 0; u < kBp3SV; ++u) xs_cur[u] = xs_nxt[u];
+    v_cur = v_nxt;
+    n_lo = f_lo;
+    n_hi = f_hi;
+    v_nxt = v_far;
     id += stride;
-    s ^= 1;
+    slot ^= 1;
   }
 
   uint64_t v[5] = {acc_n, acc_key, acc_rr, acc_rs, acc_mix};
@@ -1390,7 +1156,7 @@ __global__ void __launch_bounds__(kBp2TPB, 1) k_build_probe2(BuildProbeArgs a) {
   __syncthreads();
   if (tid < 5) {
     unsigned long long sum = 0;
-    for (int w = 0; w < kBp2TPB / 32; ++w) sum += s_red[tid][w];
+    for (int w = 0; w < TPB / 32; ++w) sum += s_red[tid][w];
     if (sum) atomicAdd(&a.result[tid], sum);
   }
 }
