@@ -289,7 +289,7 @@ def run_ours(args):
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_scatter_network_bytes_per_launch")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "k_scatter<InputSource<16>> (network partitioning pass)",
+    roofline = {"bound": "hbm", "kernel": "k_scatter3<InputSource<16>> (network partitioning pass)",
                 "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": net_bytes, "launch_us": net_launch_us}

@@ -14,11 +14,21 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _free_port():
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    p = s.getsockname()[1]
-    s.close()
-    return p
+    """A port nobody listens on right now, away from the ephemeral range the OS hands out
+    (a port obtained with bind(0) can be re-used by an outgoing connection before the
+    rendezvous store binds it)."""
+    import random
+    for _ in range(64):
+        p = random.randint(20000, 29999)
+        s = socket.socket()
+        try:
+            s.bind(("127.0.0.1", p))
+            return p
+        except OSError:
+            continue
+        finally:
+            s.close()
+    raise RuntimeError("no free port")
 
 
 def _worker(rank, world, port, per, knobs, out_dir):
