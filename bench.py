@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk", type=int, default=0)
+    ap.add_argument("--net-bits", type=int, default=0, help="network radix bits (0 = by GPU count)")
+    ap.add_argument("--loc-bits", type=int, default=0, help="local radix bits (0 = by GPU count)")
     ap.add_argument("--agg", action="store_true", help="warp-aggregated histogram atomics")
     return ap.parse_args()
 
@@ -205,7 +207,12 @@ def run_ours(args):
     n = 1 << args.log2n          # tuples per relation per GPU
     G = n * world                # global relation size
     flags = (rhj.FLAG_HIST_WARP_AGGREGATE if args.agg else 0) | (rhj.FLAG_STAGE_HOST_INPUTS if world == 1 else 0)
-    cfg = rhj.make_config(8, 8, 24, True, tuple_bytes=16, chunk_tuples=args.chunk, flags=flags)
+    # radix bits: sub-partitions of ~4096 build tuples (one shared-memory table) need
+    # log2(global size / 4096) bits in total; weak scaling adds log2(N) bits
+    default_bits = {1: (8, 8), 2: (8, 9), 4: (9, 9), 8: (9, 10)}.get(world, (9, 10))
+    net_bits = args.net_bits or default_bits[0]
+    loc_bits = args.loc_bits or default_bits[1]
+    cfg = rhj.make_config(net_bits, loc_bits, 32 - net_bits, True, tuple_bytes=16, chunk_tuples=args.chunk, flags=flags)
 
     # synthetic relations, generated on the device (harness generator, bit-identical to the oracle's)
     d_inner = torch.empty(2 * n, dtype=torch.int64, device=dev)
@@ -353,9 +360,10 @@ def run_ours(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
                 "config": {"workload": f"{n} x {n} 16-byte tuples per GPU (global {G} x {G}), unique keys, 1:1 FK, "
                                        f"counter-based generator; BASELINE configs[{1 if world == 1 else 2}]",
-                           "radix_bits": "8 network + 8 local", "tuple_bytes": 16,
+                           "radix_bits": f"{net_bits} network + {loc_bits} local", "tuple_bytes": 16,
                            "l2": "inputs (8 GiB per GPU) are larger than L2; no flush needed",
-                           "exchange": "none (1 GPU)" if world == 1 else "P2P stores over NVLink (CUDA IPC windows)"},
+                           "exchange": "none (1 GPU)" if world == 1 else
+                           "local send buffers pushed with coalesced P2P stores over NVLink (CUDA IPC windows)"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "stages": stages, "cpu_baseline": cpu,
                 "result": {"matches": G, "checksum_ok": True}}

@@ -98,6 +98,13 @@ struct rhj_ctx {
   int *d_status = nullptr;
   ItemDesc *d_items = nullptr;
   uint64_t items_cap = 0;
+  // staged exchange (nranks > 1)
+  uint64_t *sendbuf[2] = {nullptr, nullptr};
+  uint64_t *d_push_src = nullptr, *d_push_dst = nullptr, *d_push_cnt = nullptr;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_scattered = nullptr, ev_pushed = nullptr;
+  bool staged_exchange = false;
+  int reserve_sms = 0, tune_push_sms = 32;
 
   // peers (data/Window.cpp: target of MPI_Put)
   uint64_t peer_window[2][kMaxRanks] = {};
@@ -185,6 +192,13 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = std::max(0, std::min(32, atoi(e)));
   if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
   if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
+  c->staged_exchange = nranks > 1 && !getenv("RHJ_DIRECT_P2P");
+  if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
+  if (c->staged_exchange) {
+    RHJ_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_scattered, cudaEventDisableTiming));
+    RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_pushed, cudaEventDisableTiming));
+  }
   if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
   *out = c;
   return RHJ_OK;
@@ -209,6 +223,9 @@ extern "C" int rhj_destroy(rhj_ctx *ctx) {
   rhj_pool_free_all(ctx);
   for (int i = 0; i < EV_COUNT; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  if (ctx->ev_scattered) cudaEventDestroy(ctx->ev_scattered);
+  if (ctx->ev_pushed) cudaEventDestroy(ctx->ev_pushed);
+  if (ctx->side) cudaStreamDestroy(ctx->side);
   delete ctx;
   return RHJ_OK;
 }
@@ -298,6 +315,10 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   add(NS * 8); add((uint64_t)nowned * 8); add(((uint64_t)nowned + 1) * 8);  // item_lstart, jcount, jstart
   add(8); add(5 * 8); add(4);                      // work counter, result, status
   add((NS + kItemSlack) * sizeof(ItemDesc));       // expanded build/probe work list
+  if (nranks > 1) {                                // send buffers + push lists of the staged exchange
+    add(max_local[0] * 8); add(max_local[1] * 8);
+    for (int i = 0; i < 3; ++i) add(2ull * P * 8);
+  }
   lay->total = total;
 }
 
@@ -384,6 +405,12 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (!rc) rc = carve(ctx, 1ull, &ctx->d_status);
   ctx->items_cap = NS + kItemSlack;
   if (!rc) rc = carve(ctx, ctx->items_cap, &ctx->d_items);
+  if (ctx->nranks > 1) {
+    for (int k = 0; k < 2 && !rc; ++k) rc = carve(ctx, ml[k], &ctx->sendbuf[k]);
+    if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_push_src);
+    if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_push_dst);
+    if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_push_cnt);
+  }
   if (rc) return rc;
   RHJ_CUDA(cudaMemset(ctx->d_status, 0, sizeof(int)));
   RHJ_CUDA(cudaMemset(ctx->d_result, 0, 5 * 8));
@@ -489,7 +516,8 @@ static int launch_scatter3(rhj_ctx *ctx, const Source &src, const Map &cm, uint3
   int per_sm = 0;
   RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem));
   if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
-  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count * per_sm));
+  // reserve_sms: leave some SMs to a concurrently running push kernel (staged exchange)
+  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)((ctx->sm_count - ctx->reserve_sms) * per_sm));
   kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ctx->tiles_per_chunk, chunk_off, tile_off, tile_start, bin_base,
                                 ctx->d_status, ctx->tune_l2_ahead);
   RHJ_CHECK_LAUNCH("k_scatter3");
@@ -593,6 +621,10 @@ extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, v
   a.cstart = ctx->d_cstart;
   a.chunk2 = ctx->chunk2;
   a.status = ctx->d_status;
+  for (int k = 0; k < 2; ++k) a.stage_base[k] = ctx->staged_exchange ? reinterpret_cast<uint64_t>(ctx->sendbuf[k]) : 0;
+  a.push_src = ctx->d_push_src;
+  a.push_dst = ctx->d_push_dst;
+  a.push_cnt = ctx->d_push_cnt;
   k_plan_network<<<1, 1024, ((size_t)ctx->P + 1) * 8, st>>>(a);
   RHJ_CHECK_LAUNCH("k_plan_network");
   int rc = record(ctx, EV_HIST, st);
@@ -609,6 +641,8 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
   for (int k = 0; k < 2; ++k) {
     ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
     int rc;
+    // while the outer relation is scattered, the inner relation's push runs on the SMs left free
+    ctx->reserve_sms = (ctx->staged_exchange && k == 1) ? ctx->tune_push_sms : 0;
     if (ctx->cfg.tuple_bytes == 16) {
       InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
       rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
@@ -617,7 +651,23 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
       rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
     }
     if (rc) return rc;
+    if (ctx->staged_exchange) {
+      // push this relation's remote partitions; the inner relation's push runs on a side
+      // stream so that it overlaps the scatter of the outer relation
+      cudaStream_t ps = k == 0 ? ctx->side : st;
+      if (k == 0) {
+        RHJ_CUDA(cudaEventRecord(ctx->ev_scattered, st));
+        RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered, 0));
+      }
+      dim3 grid(8, ctx->P);
+      k_push<<<grid, kPushTPB, 0, ps>>>(ctx->d_push_src + (uint64_t)k * ctx->P, ctx->d_push_dst + (uint64_t)k * ctx->P,
+                                        ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->d_status);
+      RHJ_CHECK_LAUNCH("k_push");
+      if (k == 0) RHJ_CUDA(cudaEventRecord(ctx->ev_pushed, ctx->side));
+      else RHJ_CUDA(cudaStreamWaitEvent(st, ctx->ev_pushed, 0));
+    }
   }
+  ctx->reserve_sms = 0;
   int rc = record(ctx, EV_NET, st);
   if (rc) return rc;
   ctx->stage = 3;

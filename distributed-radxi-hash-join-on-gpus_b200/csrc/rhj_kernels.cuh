@@ -497,6 +497,10 @@ struct PlanNetworkArgs {
   uint32_t chunk2;      // tuples per local-pass chunk
   uint32_t max_chunks2[2];
   int *status;
+  // staged exchange (nranks > 1): tuples for remote partitions are first gathered in a local
+  // send buffer, contiguous per partition, and pushed to the owner with coalesced stores
+  uint64_t stage_base[2];                  // byte address of the send buffers, 0 = store directly into peers
+  uint64_t *push_src, *push_dst, *push_cnt;  // [2][P]; cnt == 0 for partitions this rank owns
 };
 
 __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
@@ -578,6 +582,65 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
       if (ccarry > a.max_chunks2[k]) atomicMax(a.status, (int)kDevLocalOverflow);
     }
     __syncthreads();
+    if (a.stage_base[k]) {
+      // send-buffer offset of partition p = my tuples of the remote partitions before it
+      uint64_t scarry = 0;
+      for (uint32_t i0 = 0; i0 < P; i0 += blockDim.x) {
+        const uint32_t i = i0 + tid;
+        const uint64_t v = (i < P && i % n != me) ? a.gathered[((uint64_t)me * 2 + k) * P + i] : 0;
+        uint64_t total;
+        const uint64_t ex = block_exclusive_scan<uint64_t>(v, tmp64, &total);
+        if (i < P) sh_scan[i] = scarry + ex;
+        scarry += total;
+      }
+      __syncthreads();
+      for (uint32_t p = tid; p < P; p += blockDim.x) {
+        const bool remote = p % n != me;
+        const uint64_t src = a.stage_base[k] + sh_scan[p] * 8;
+        a.push_cnt[k * P + p] = remote ? a.gathered[((uint64_t)me * 2 + k) * P + p] : 0;
+        a.push_src[k * P + p] = src;
+        a.push_dst[k * P + p] = a.dest[k * P + p];
+        if (remote) a.dest[k * P + p] = src;  // the scatter kernel fills the send buffer instead
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// Push: copy every remote partition's run from the local send buffer into the owner's
+// window (replaces MPI_Put, data/Window.cpp:108-115).  grid = (slices, P).  Runs are
+// megabytes long and contiguous on both sides, so each warp store covers whole 128-byte
+// lines of the peer's memory: NVLink sees full-line writes instead of the 8-byte-granular
+// runs the scatter kernel would produce.
+// ---------------------------------------------------------------------------------
+constexpr int kPushTPB = 256;
+__global__ void __launch_bounds__(kPushTPB) k_push(const uint64_t *__restrict__ src_addr,
+                                                    const uint64_t *__restrict__ dst_addr,
+                                                    const uint64_t *__restrict__ cnt,
+                                                    const int *__restrict__ status) {
+  if (*status != kDevOk) return;
+  const uint32_t p = blockIdx.y;
+  const uint64_t n = cnt[p];
+  if (n == 0) return;
+  const uint64_t *src = reinterpret_cast<const uint64_t *>(src_addr[p]);
+  uint64_t *dst = reinterpret_cast<uint64_t *>(dst_addr[p]);
+  // head: up to the first 128-byte boundary of the destination (CTA 0), then equal slices of whole lines
+  uint64_t head = ((128 - (dst_addr[p] & 127)) & 127) / 8;
+  if (head > n) head = n;
+  if (blockIdx.x == 0 && threadIdx.x < head) dst[threadIdx.x] = ld_stream_u64(src + threadIdx.x);
+  const uint64_t body = n - head;
+  const uint64_t per = ((body + gridDim.x - 1) / gridDim.x + 15) & ~uint64_t(15);
+  const uint64_t b = head + (uint64_t)blockIdx.x * per;
+  const uint64_t e = b + per < n ? b + per : n;
+  for (uint64_t i = b + threadIdx.x; i < e; i += (uint64_t)kPushTPB * 4) {
+    uint64_t v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + (uint64_t)u * kPushTPB < e) v[u] = ld_stream_u64(src + i + (uint64_t)u * kPushTPB);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + (uint64_t)u * kPushTPB < e) st_stream_u64(dst + i + (uint64_t)u * kPushTPB, v[u]);
   }
 }
 
