@@ -101,6 +101,8 @@ SYMBOLS = {
     "rhj_get_write_offsets": (_int, [_vp, _int, _vp, _vp]),
     "rhj_network_partition": (_int, [_vp, _vp]),
     "rhj_local_partition": (_int, [_vp, _vp]),
+    "rhj_exchange_wait": (_int, [_vp, _int, _vp]),
+    "rhj_local_partition_rel": (_int, [_vp, _int, _vp]),
     "rhj_get_local_partition": (_int, [_vp, _int, _u32, _vp, _vp, _vp]),
     "rhj_get_partition_dev": (_int, [_vp, _int, _u32, _int, C.POINTER(_vp), C.POINTER(_u64)]),
     "rhj_build_probe": (_int, [_vp, _vp]),
@@ -244,6 +246,12 @@ class Context:
 
     def local_partition(self):
         check(lib().rhj_local_partition(self.h, _stream()))
+
+    def exchange_wait(self, which: int):
+        check(lib().rhj_exchange_wait(self.h, which, _stream()))
+
+    def local_partition_rel(self, which: int):
+        check(lib().rhj_local_partition_rel(self.h, which, _stream()))
 
     def build_probe(self):
         check(lib().rhj_build_probe(self.h, _stream()))

@@ -102,7 +102,8 @@ struct rhj_ctx {
   uint64_t *sendbuf[2] = {nullptr, nullptr};
   uint64_t *d_push_src = nullptr, *d_push_dst = nullptr, *d_push_cnt = nullptr;
   cudaStream_t side = nullptr;
-  cudaEvent_t ev_scattered = nullptr, ev_pushed = nullptr;
+  cudaEvent_t ev_scattered[2] = {nullptr, nullptr}, ev_pushed[2] = {nullptr, nullptr};
+  bool rel_partitioned[2] = {false, false};
   bool staged_exchange = false;
   int reserve_sms = 0, tune_push_sms = 32;
 
@@ -196,8 +197,10 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
   if (c->staged_exchange) {
     RHJ_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
-    RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_scattered, cudaEventDisableTiming));
-    RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_pushed, cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k) {
+      RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_scattered[k], cudaEventDisableTiming));
+      RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_pushed[k], cudaEventDisableTiming));
+    }
   }
   if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
   *out = c;
@@ -223,8 +226,10 @@ extern "C" int rhj_destroy(rhj_ctx *ctx) {
   rhj_pool_free_all(ctx);
   for (int i = 0; i < EV_COUNT; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
-  if (ctx->ev_scattered) cudaEventDestroy(ctx->ev_scattered);
-  if (ctx->ev_pushed) cudaEventDestroy(ctx->ev_pushed);
+  for (int k = 0; k < 2; ++k) {
+    if (ctx->ev_scattered[k]) cudaEventDestroy(ctx->ev_scattered[k]);
+    if (ctx->ev_pushed[k]) cudaEventDestroy(ctx->ev_pushed[k]);
+  }
   if (ctx->side) cudaStreamDestroy(ctx->side);
   delete ctx;
   return RHJ_OK;
@@ -577,6 +582,7 @@ extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner
   ctx->input_n[1] = outer_n;
   for (int k = 0; k < 2; ++k) ctx->nchunks1[k] = (uint32_t)((ctx->input_n[k] + ctx->chunk1 - 1) / ctx->chunk1);
   ctx->local_planned = false;
+  ctx->rel_partitioned[0] = ctx->rel_partitioned[1] = false;
   int rc = record(ctx, EV_START, st);
   if (rc) return rc;
   RHJ_CUDA(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), st));
@@ -652,19 +658,16 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
     }
     if (rc) return rc;
     if (ctx->staged_exchange) {
-      // push this relation's remote partitions; the inner relation's push runs on a side
-      // stream so that it overlaps the scatter of the outer relation
-      cudaStream_t ps = k == 0 ? ctx->side : st;
-      if (k == 0) {
-        RHJ_CUDA(cudaEventRecord(ctx->ev_scattered, st));
-        RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered, 0));
-      }
+      // push this relation's remote partitions on the side stream: the inner relation's push
+      // overlaps the scatter of the outer relation, the outer relation's push overlaps the
+      // local pass of the inner one (rhj_exchange_wait / rhj_local_partition_rel order the rest)
+      RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
+      RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
       dim3 grid(8, ctx->P);
-      k_push<<<grid, kPushTPB, 0, ps>>>(ctx->d_push_src + (uint64_t)k * ctx->P, ctx->d_push_dst + (uint64_t)k * ctx->P,
-                                        ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->d_status);
+      k_push<<<grid, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P, ctx->d_push_dst + (uint64_t)k * ctx->P,
+                                               ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->d_status);
       RHJ_CHECK_LAUNCH("k_push");
-      if (k == 0) RHJ_CUDA(cudaEventRecord(ctx->ev_pushed, ctx->side));
-      else RHJ_CUDA(cudaStreamWaitEvent(st, ctx->ev_pushed, 0));
+      RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
     }
   }
   ctx->reserve_sms = 0;
@@ -674,7 +677,7 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
   return RHJ_OK;
 }
 
-static int launch_plan_local(rhj_ctx *ctx, cudaStream_t st) {
+static int launch_plan_local(rhj_ctx *ctx, int k_begin, int k_end, bool do_items, cudaStream_t st) {
   if (ctx->nowned == 0) {
     RHJ_CUDA(cudaMemsetAsync(ctx->d_item_jstart, 0, 8, st));
     ctx->local_planned = true;
@@ -699,48 +702,75 @@ static int launch_plan_local(rhj_ctx *ctx, cudaStream_t st) {
   a.item_jcount = ctx->d_item_jcount;
   a.cap_r = ctx->cap_r;
   a.sslice = ctx->sslice;
+  a.k_begin = k_begin;
+  a.k_end = k_end;
+  a.do_items = do_items ? 1 : 0;
   k_plan_local<<<ctx->nowned, 256, 0, st>>>(a);
   RHJ_CHECK_LAUNCH("k_plan_local");
-  k_plan_items<<<1, 1024, 0, st>>>(ctx->d_item_jcount, ctx->nowned, ctx->d_item_jstart, ctx->d_work);
-  RHJ_CHECK_LAUNCH("k_plan_items");
-  ctx->local_planned = true;
+  if (do_items) {
+    k_plan_items<<<1, 1024, 0, st>>>(ctx->d_item_jcount, ctx->nowned, ctx->d_item_jstart, ctx->d_work);
+    RHJ_CHECK_LAUNCH("k_plan_items");
+    ctx->local_planned = true;
+  }
+  return RHJ_OK;
+}
+
+// Make `stream` wait until this rank's pushes of relation `which` have been issued and completed.
+extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  if (ctx->staged_exchange) {
+    RHJ_CUDA(cudaSetDevice(ctx->device));
+    RHJ_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), ctx->ev_pushed[which], 0));
+  }
+  return RHJ_OK;
+}
+
+extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = rhj_exchange_wait(ctx, which, stream);  // this rank's own pushes of the relation are done
+  if (rc) return rc;
+  const int k = which;
+  const bool other_done = ctx->rel_partitioned[k ^ 1];
+  if (ctx->cfg.enable_two_level && ctx->nowned > 0) {
+    const uint32_t L = ctx->L;
+    // while the other relation is still being pushed, leave it some SMs
+    ctx->reserve_sms = (ctx->staged_exchange && !other_done) ? ctx->tune_push_sms : 0;
+    ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
+    ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
+                   ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
+    rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
+                          ctx->tile2_start[k], st);
+    if (rc) return rc;
+    dim3 grid((L + 31) / 32, ctx->nowned);
+    k_colscan<8><<<grid, 8 * 32, 0, st>>>(ctx->chunk2_hist[k], L, ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), 0,
+                                           ctx->d_sub_tot + (uint64_t)k * ctx->NS, ctx->d_status);
+    RHJ_CHECK_LAUNCH("k_colscan(local)");
+    rc = launch_plan_local(ctx, k, k + 1, other_done, st);
+    if (rc) return rc;
+    rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
+                        ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
+    ctx->reserve_sms = 0;
+    if (rc) return rc;
+  }
+  ctx->rel_partitioned[k] = true;
+  if (other_done) {
+    rc = record(ctx, EV_LOCAL, st);
+    if (rc) return rc;
+    ctx->stage = 4;
+  }
   return RHJ_OK;
 }
 
 extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
-  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
-  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
-  RHJ_CUDA(cudaSetDevice(ctx->device));
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (ctx->cfg.enable_two_level && ctx->nowned > 0) {
-    const uint32_t L = ctx->L;
-    for (int k = 0; k < 2; ++k) {
-      ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
-      ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
-                     ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
-      int rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
-                                ctx->tile2_start[k], st);
-      if (rc) return rc;
-      dim3 grid((L + 31) / 32, ctx->nowned);
-      k_colscan<8><<<grid, 8 * 32, 0, st>>>(ctx->chunk2_hist[k], L, ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), 0,
-                                             ctx->d_sub_tot + (uint64_t)k * ctx->NS, ctx->d_status);
-      RHJ_CHECK_LAUNCH("k_colscan(local)");
-    }
-    int rc = launch_plan_local(ctx, st);
-    if (rc) return rc;
-    for (int k = 0; k < 2; ++k) {
-      ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
-      ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
-                     ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
-      rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
-                          ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
-      if (rc) return rc;
-    }
-  }
-  int rc = record(ctx, EV_LOCAL, st);
-  if (rc) return rc;
-  ctx->stage = 4;
-  return RHJ_OK;
+  int rc = rhj_local_partition_rel(ctx, 0, stream);
+  if (!rc) rc = rhj_local_partition_rel(ctx, 1, stream);
+  return rc;
 }
 
 template <int CAP>
@@ -790,7 +820,7 @@ extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) {
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (!ctx->local_planned) {
-    int rc = launch_plan_local(ctx, st);
+    int rc = launch_plan_local(ctx, 0, 2, true, st);
     if (rc) return rc;
   }
   if (ctx->nowned > 0) {

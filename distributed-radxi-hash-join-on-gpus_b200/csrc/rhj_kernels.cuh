@@ -775,6 +775,8 @@ struct PlanLocalArgs {
   uint64_t *item_lstart;     // [nowned*L] exclusive item prefix inside partition j
   uint64_t *item_jcount;     // [nowned]
   uint32_t cap_r, sslice;
+  int k_begin, k_end;  // relations laid out by this launch
+  int do_items;        // also emit the work list (needs sub_cnt of BOTH relations in memory)
 };
 
 __global__ void __launch_bounds__(256) k_plan_local(PlanLocalArgs a) {
@@ -786,6 +788,10 @@ __global__ void __launch_bounds__(256) k_plan_local(PlanLocalArgs a) {
     uint32_t l = l0 + tid;
     uint32_t cnt[2] = {0, 0};
     for (int k = 0; k < 2; ++k) {
+      if (k < a.k_begin || k >= a.k_end) {  // laid out by an earlier launch: only its counts are needed
+        if (l < L && a.do_items) cnt[k] = a.sub_cnt[(uint64_t)k * NS + (uint64_t)j * L + l];
+        continue;
+      }
       uint64_t c = 0;
       if (l < L) c = a.two_level ? a.sub_tot[(uint64_t)k * NS + (uint64_t)j * L + l] : a.part_cnt[k * a.nowned + j];
       cnt[k] = (uint32_t)c;
@@ -803,6 +809,7 @@ __global__ void __launch_bounds__(256) k_plan_local(PlanLocalArgs a) {
       }
       pcarry[k] += total;
     }
+    if (!a.do_items) continue;
     uint64_t items = 0;
     if (l < L && cnt[0] > 0 && cnt[1] > 0)
       items = (uint64_t)((cnt[0] + a.cap_r - 1) / a.cap_r) * (uint64_t)((cnt[1] + a.sslice - 1) / a.sslice);
@@ -811,7 +818,7 @@ __global__ void __launch_bounds__(256) k_plan_local(PlanLocalArgs a) {
     if (l < L) a.item_lstart[(uint64_t)j * L + l] = icarry + iex;
     icarry += itotal;
   }
-  if (tid == 0) a.item_jcount[j] = icarry;
+  if (tid == 0 && a.do_items) a.item_jcount[j] = icarry;
 }
 
 // exclusive scan of item_jcount -> item_jstart[nowned+1]; resets the work counter and result

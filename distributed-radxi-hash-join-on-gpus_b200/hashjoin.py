@@ -76,10 +76,16 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None):
         ctx.compute_offsets(None)
     ctx.network_partition()
     if ctx.nranks > 1:
-        # all peer stores have been issued before any rank reads its window
+        # Per relation: my pushes are complete (exchange_wait), then everybody's are (the
+        # all-reduce is the barrier of operators/HashJoin.cpp:119-121).  The inner relation's
+        # local pass then runs while the outer relation is still crossing NVLink.
         token = torch.zeros(1, dtype=torch.int32, device=f"cuda:{ctx.device}")
-        dist.all_reduce(token, group=group)
-    ctx.local_partition()
+        for which in (0, 1):
+            ctx.exchange_wait(which)
+            dist.all_reduce(token, group=group)
+            ctx.local_partition_rel(which)
+    else:
+        ctx.local_partition()
     ctx.build_probe()
 
 

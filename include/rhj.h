@@ -158,6 +158,15 @@ int rhj_network_partition(rhj_ctx *ctx, void *stream);
 /* TASK_PARTITION -- tasks/LocalPartitioning.cpp:59-250 for every owned partition:
  * histogram, 8-tuple padded prefix, scatter.  No-op unless enable_two_level. */
 int rhj_local_partition(rhj_ctx *ctx, void *stream);
+/* The same, one relation at a time (which: 0 inner, 1 outer), so that a multi-rank launcher can
+ * start the inner relation's local pass while the outer relation is still crossing NVLink:
+ *   rhj_network_partition -> rhj_exchange_wait(0) -> barrier -> rhj_local_partition_rel(0)
+ *                         -> rhj_exchange_wait(1) -> barrier -> rhj_local_partition_rel(1) -> rhj_build_probe
+ * rhj_exchange_wait makes `stream` wait until THIS rank's stores of relation `which` into its
+ * peers' windows are complete (MPI_Win_flush_local_all, data/Window.cpp:193-201); the barrier
+ * that follows (operators/HashJoin.cpp:119-121) then means every rank's are. */
+int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream);
+int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream);
 /* tasks/LocalPartitioning.cpp:138-192 results for owned partition `p` (host copies). */
 int rhj_get_local_partition(rhj_ctx *ctx, int which, uint32_t p, uint64_t *hist_host, uint64_t *prefix_host,
                             void *stream);
