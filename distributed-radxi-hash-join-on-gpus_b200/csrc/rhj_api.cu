@@ -493,7 +493,7 @@ static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint
     // few replicas: every replica has to be summed per tile, and 256 random bins rarely collide
     uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, (256u * ctx->tune_hist_rep) / nbins));
     size_t smem = ((size_t)2 * nbins * nrep + nbins + 80) * 4;
-    uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 4);
+    uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count - ctx->reserve_sms) * 4);
     k_histogram_tiles<Source, Map><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, ctx->tiles_per_chunk, chunk_hist,
                                                                   tile_off, tile_start, ctx->d_status);
     RHJ_CHECK_LAUNCH("k_histogram_tiles");
@@ -663,9 +663,10 @@ extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
       // local pass of the inner one (rhj_exchange_wait / rhj_local_partition_rel order the rest)
       RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
       RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
-      dim3 grid(8, ctx->P);
-      k_push<<<grid, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P, ctx->d_push_dst + (uint64_t)k * ctx->P,
-                                               ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->d_status);
+      const uint32_t push_ctas = (uint32_t)std::max(8, ctx->tune_push_sms * 8);
+      k_push<<<push_ctas, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P,
+                                                    ctx->d_push_dst + (uint64_t)k * ctx->P,
+                                                    ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->P, ctx->d_status);
       RHJ_CHECK_LAUNCH("k_push");
       RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
     }

@@ -609,7 +609,7 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
 
 // ---------------------------------------------------------------------------------
 // Push: copy every remote partition's run from the local send buffer into the owner's
-// window (replaces MPI_Put, data/Window.cpp:108-115).  grid = (slices, P).  Runs are
+// window (replaces MPI_Put, data/Window.cpp:108-115).  Runs are
 // megabytes long and contiguous on both sides, so each warp store covers whole 128-byte
 // lines of the peer's memory: NVLink sees full-line writes instead of the 8-byte-granular
 // runs the scatter kernel would produce.
@@ -617,30 +617,37 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
 constexpr int kPushTPB = 256;
 __global__ void __launch_bounds__(kPushTPB) k_push(const uint64_t *__restrict__ src_addr,
                                                     const uint64_t *__restrict__ dst_addr,
-                                                    const uint64_t *__restrict__ cnt,
+                                                    const uint64_t *__restrict__ cnt, const uint32_t nparts,
                                                     const int *__restrict__ status) {
+  // Persistent and deliberately small grid (a few CTAs on the SMs the concurrent scatter or
+  // local-pass kernel leaves free): a push that floods every SM with resident CTAs starves
+  // whatever is launched next -- the barrier's NCCL kernel waited 0.7 ms for a slot.
   if (*status != kDevOk) return;
-  const uint32_t p = blockIdx.y;
-  const uint64_t n = cnt[p];
-  if (n == 0) return;
-  const uint64_t *src = reinterpret_cast<const uint64_t *>(src_addr[p]);
-  uint64_t *dst = reinterpret_cast<uint64_t *>(dst_addr[p]);
-  // head: up to the first 128-byte boundary of the destination (CTA 0), then equal slices of whole lines
-  uint64_t head = ((128 - (dst_addr[p] & 127)) & 127) / 8;
-  if (head > n) head = n;
-  if (blockIdx.x == 0 && threadIdx.x < head) dst[threadIdx.x] = ld_stream_u64(src + threadIdx.x);
-  const uint64_t body = n - head;
-  const uint64_t per = ((body + gridDim.x - 1) / gridDim.x + 15) & ~uint64_t(15);
-  const uint64_t b = head + (uint64_t)blockIdx.x * per;
-  const uint64_t e = b + per < n ? b + per : n;
-  for (uint64_t i = b + threadIdx.x; i < e; i += (uint64_t)kPushTPB * 4) {
-    uint64_t v[4];
+  constexpr uint32_t kSlice = 8192;  // tuples per work item (64 KB)
+  for (uint32_t p = 0; p < nparts; ++p) {
+    const uint64_t n = cnt[p];
+    if (n == 0) continue;
+    const uint64_t *src = reinterpret_cast<const uint64_t *>(src_addr[p]);
+    uint64_t *dst = reinterpret_cast<uint64_t *>(dst_addr[p]);
+    // head: up to the first 128-byte boundary of the destination, then slices of whole lines
+    uint64_t head = ((128 - (dst_addr[p] & 127)) & 127) / 8;
+    if (head > n) head = n;
+    if (blockIdx.x == p % gridDim.x && threadIdx.x < head) dst[threadIdx.x] = ld_stream_u64(src + threadIdx.x);
+    const uint64_t nslices = (n - head + kSlice - 1) / kSlice;
+    // start each partition at a different CTA so that short runs do not all land on CTA 0
+    for (uint64_t sl = (blockIdx.x + gridDim.x - p % gridDim.x) % gridDim.x; sl < nslices; sl += gridDim.x) {
+      const uint64_t b = head + sl * kSlice;
+      const uint64_t e = b + kSlice < n ? b + kSlice : n;
+      for (uint64_t i = b + threadIdx.x; i < e; i += (uint64_t)kPushTPB * 8) {
+        uint64_t v[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (i + (uint64_t)u * kPushTPB < e) v[u] = ld_stream_u64(src + i + (uint64_t)u * kPushTPB);
+        for (int u = 0; u < 8; ++u)
+          if (i + (uint64_t)u * kPushTPB < e) v[u] = ld_stream_u64(src + i + (uint64_t)u * kPushTPB);
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (i + (uint64_t)u * kPushTPB < e) st_stream_u64(dst + i + (uint64_t)u * kPushTPB, v[u]);
+        for (int u = 0; u < 8; ++u)
+          if (i + (uint64_t)u * kPushTPB < e) st_stream_u64(dst + i + (uint64_t)u * kPushTPB, v[u]);
+      }
+    }
   }
 }
 
