@@ -102,6 +102,7 @@ SYMBOLS = {
     "rhj_network_partition": (_int, [_vp, _vp]),
     "rhj_local_partition": (_int, [_vp, _vp]),
     "rhj_exchange_wait": (_int, [_vp, _int, _vp]),
+    "rhj_exchange_sync": (_int, [_vp, _int]),
     "rhj_local_partition_rel": (_int, [_vp, _int, _vp]),
     "rhj_get_local_partition": (_int, [_vp, _int, _u32, _vp, _vp, _vp]),
     "rhj_get_partition_dev": (_int, [_vp, _int, _u32, _int, C.POINTER(_vp), C.POINTER(_u64)]),
@@ -249,6 +250,9 @@ class Context:
 
     def exchange_wait(self, which: int):
         check(lib().rhj_exchange_wait(self.h, which, _stream()))
+
+    def exchange_sync(self, which: int):
+        check(lib().rhj_exchange_sync(self.h, which))
 
     def local_partition_rel(self, which: int):
         check(lib().rhj_local_partition_rel(self.h, which, _stream()))

@@ -148,7 +148,7 @@ static int validate_config(const rhj_config *c, int rank, int nranks) {
   if (cap != 1024 && cap != 2048 && cap != 4096 && cap != 8192)
     return fail(RHJ_ERR_INVALID, "build_capacity must be 1024, 2048, 4096 or 8192");
   uint32_t chunk = c->chunk_tuples ? c->chunk_tuples : kDefaultChunk;
-  if (chunk % kScatTile != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kScatTile);
+  if (chunk % kTile != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kTile);
   return RHJ_OK;
 }
 
@@ -183,7 +183,7 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   c->chunk1 = c->chunk2 = cfg->chunk_tuples ? cfg->chunk_tuples : kDefaultChunk;
   c->cap_r = cfg->build_capacity ? cfg->build_capacity : kDefaultBuildCap;
   c->sslice = 4 * c->cap_r;
-  c->tiles_per_chunk = c->chunk1 / kScatTile;
+  c->tiles_per_chunk = c->chunk1 / kTile;
   cudaDeviceProp prop;
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
@@ -302,7 +302,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
     if (cfg->flags & RHJ_FLAG_STAGE_HOST_INPUTS) add(max_local[k] * cfg->tuple_bytes);
     add((uint64_t)lay->max_chunks1[k] * P * 4);
     if (cfg->enable_two_level) add((uint64_t)lay->max_chunks2[k] * L * 4);
-    const uint64_t tpc = chunk / kScatTile;
+    const uint64_t tpc = chunk / kTile;
     add((uint64_t)lay->max_chunks1[k] * tpc * P * 4);
     add((uint64_t)lay->max_chunks1[k] * tpc * P * 2);
     if (cfg->enable_two_level) {
@@ -725,6 +725,17 @@ extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
     RHJ_CUDA(cudaSetDevice(ctx->device));
     RHJ_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), ctx->ev_pushed[which], 0));
   }
+  return RHJ_OK;
+}
+
+// Host-blocking form: returns when this rank's pushes of relation `which` are complete.
+extern "C" int rhj_exchange_sync(rhj_ctx *ctx, int which) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  if (ctx->staged_exchange) RHJ_CUDA(cudaEventSynchronize(ctx->ev_pushed[which]));
+  else RHJ_CUDA(cudaEventSynchronize(ctx->ev[EV_NET]));
   return RHJ_OK;
 }
 

@@ -23,6 +23,8 @@ constexpr int kHistUnroll = 8;
 constexpr int kScatTPB = 512;
 constexpr int kScatIPT = 8;
 constexpr int kScatTile = kScatTPB * kScatIPT;  // tuples staged in shared memory per tile
+constexpr int kTile = 8192;                      // tuples per tile of the offset-driven kernels
+constexpr int kTileUnroll = kTile / kHistTPB;
 constexpr uint32_t kInvalidDigit = 0xFFFFFFFFu;
 constexpr int kScatL2Ahead = 3;  // tiles between the register prefetch and the L2 prefetch
 
@@ -175,9 +177,9 @@ __global__ void __launch_bounds__(kHistTPB) k_histogram(Source src, Map cm, uint
 //   tile_off   [row][nbins]   u32   tuples of the bin in EARLIER tiles of the same chunk
 //   tile_start [row][nbins]   u16   exclusive prefix over the bins inside the tile
 //                                   (= where the bin's run starts in the sorted tile)
-// row = chunk * tiles_per_chunk + tile; a tile is kScatTile tuples.
+// row = chunk * tiles_per_chunk + tile; a tile is kTile tuples.
 // ---------------------------------------------------------------------------------
-static_assert(kHistTPB * kHistUnroll == kScatTile, "histogram tile must equal the scatter tile");
+static_assert(kHistTPB * kTileUnroll == kTile, "histogram tile must equal the scatter tile");
 
 template <class Source, class Map>
 __global__ void __launch_bounds__(kHistTPB, 4) k_histogram_tiles(Source src, Map cm, uint32_t nbins, uint32_t nrep,
@@ -202,17 +204,17 @@ __global__ void __launch_bounds__(kHistTPB, 4) k_histogram_tiles(Source src, Map
     uint32_t seg;
     cm.range(c, b, e, seg);
     uint64_t row = (uint64_t)c * tiles_per_chunk;
-    for (uint64_t base = b; base < e; base += kScatTile, ++row, par ^= 1) {
+    for (uint64_t base = b; base < e; base += kTile, ++row, par ^= 1) {
       uint32_t *set = sh_hist + par * nrep * nbins;
       uint32_t *my = set + (warp % nrep) * nbins;
-      uint32_t dg[kHistUnroll];
+      uint32_t dg[kTileUnroll];
 #pragma unroll
-      for (int u = 0; u < kHistUnroll; ++u) {
+      for (int u = 0; u < kTileUnroll; ++u) {
         uint64_t i = base + (uint64_t)u * kHistTPB + tid;
         dg[u] = i < e ? src.digit(i) : kInvalidDigit;
       }
 #pragma unroll
-      for (int u = 0; u < kHistUnroll; ++u)
+      for (int u = 0; u < kTileUnroll; ++u)
         if (dg[u] != kInvalidDigit) atomicAdd(&my[dg[u]], 1u);
       __syncthreads();
       if (fast) {
@@ -280,7 +282,7 @@ __global__ void __launch_bounds__(kHistTPB, 4) k_histogram_tiles(Source src, Map
 // ---------------------------------------------------------------------------------
 template <class Source>
 __host__ __device__ inline size_t scatter3_smem_bytes(uint32_t nbins) {
-  return 2 * (size_t)kScatTile * 8 + (Source::kDigitFromValue ? 0 : 2 * (size_t)kScatTile * 2) +
+  return 2 * (size_t)kTile * 8 + (Source::kDigitFromValue ? 0 : 2 * (size_t)kTile * 2) +
          3 * (size_t)nbins * (8 + 4) + 64;
 }
 
@@ -291,8 +293,8 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
                const uint16_t *__restrict__ tile_start, const uint64_t *__restrict__ bin_base,
                const int *__restrict__ status, const int l2_ahead) {
   using Raw = typename Source::Raw;
-  constexpr int IPT = kScatTile / TPB;
-  constexpr uint32_t T = kScatTile;
+  constexpr int IPT = kTile / TPB;
+  constexpr uint32_t T = kTile;
   extern __shared__ __align__(128) unsigned char sh_raw[];
   if (*status != kDevOk) return;
   uint64_t *const stage = reinterpret_cast<uint64_t *>(sh_raw);           // [2][T]

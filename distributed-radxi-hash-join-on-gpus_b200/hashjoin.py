@@ -62,6 +62,25 @@ def exchange_windows(ctx, group=None):
             ctx.window_import(r, WindowHandle.from_buffer_copy(raw))
 
 
+_HOST_GROUPS = {}
+
+
+def _host_barrier_group(group=None):
+    """A gloo group over the same ranks, for barriers that must not travel over NVLink."""
+    import os
+    import torch.distributed as dist
+    if os.environ.get("RHJ_NCCL_BARRIER"):
+        return None
+    key = id(group)
+    if key not in _HOST_GROUPS:
+        try:
+            ranks = dist.get_process_group_ranks(group) if group is not None else None
+            _HOST_GROUPS[key] = dist.new_group(ranks=ranks, backend="gloo")
+        except Exception:
+            _HOST_GROUPS[key] = None
+    return _HOST_GROUPS[key]
+
+
 def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None):
     """operators/HashJoin.cpp:45-220 for this rank; every rank calls it (collective)."""
     import torch
@@ -79,10 +98,17 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None):
         # Per relation: my pushes are complete (exchange_wait), then everybody's are (the
         # all-reduce is the barrier of operators/HashJoin.cpp:119-121).  The inner relation's
         # local pass then runs while the outer relation is still crossing NVLink.
+        host_group = _host_barrier_group(group)
         token = torch.zeros(1, dtype=torch.int32, device=f"cuda:{ctx.device}")
         for which in (0, 1):
-            ctx.exchange_wait(which)
-            dist.all_reduce(token, group=group)
+            if host_group is not None:
+                # host-side barrier: a tiny NCCL collective issued while the other relation
+                # saturates NVLink waits ~1.5 ms behind that traffic (measured on 8 GPUs)
+                ctx.exchange_sync(which)
+                dist.barrier(group=host_group)
+            else:
+                ctx.exchange_wait(which)
+                dist.all_reduce(token, group=group)
             ctx.local_partition_rel(which)
     else:
         ctx.local_partition()

@@ -13,7 +13,7 @@ def cfgs(rhj):
         "shipped_one_level": rhj.make_config(5, 5, 27, False),            # core/Configuration.h as shipped
         "shipped_two_level": rhj.make_config(5, 5, 27, True),             # BASELINE config 1 knobs
         "gpu_8_8": rhj.make_config(8, 8, 24, True),                        # the B200 fan-out
-        "tiny_2_3": rhj.make_config(2, 3, 30, True, chunk_tuples=4096),
+        "tiny_2_3": rhj.make_config(2, 3, 30, True, chunk_tuples=8192),
         "wide_10_6": rhj.make_config(10, 6, 22, True, build_capacity=1024),
     }
 

@@ -86,6 +86,6 @@ def test_cuda_path_on_golden_inputs(rhj, oracle, path):
     from _util import check_against_oracle
     z, knobs, ranks, ni, no, gen = load(path)
     inner, outer = relations(z, ranks, oracle)
-    cfg = rhj.make_config(knobs[0], knobs[1], knobs[2], bool(knobs[3]), chunk_tuples=4096)
+    cfg = rhj.make_config(knobs[0], knobs[1], knobs[2], bool(knobs[3]), chunk_tuples=8192)
     res = check_against_oracle(rhj, oracle, cfg, [a.copy() for a in inner], [a.copy() for a in outer])
     assert [r.matches for r in res] == [int(m) for m in z["matches"]]

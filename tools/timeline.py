@@ -23,8 +23,14 @@ ctx.histogram(di, n, do, n)
 local = torch.as_tensor(rhj.hashjoin._DeviceArray(ctx.local_histogram_ptr(), 2 * ctx.P), device=dev)
 g = torch.empty(world * 2 * ctx.P, dtype=torch.int64, device=dev); dist.all_gather_into_tensor(g, local); ctx.compute_offsets(g)
 ev[1].record(); ctx.network_partition(); ev[2].record()
-ctx.exchange_wait(0); ev[3].record(); dist.all_reduce(tok); ev[4].record(); ctx.local_partition_rel(0); ev[5].record()
-ctx.exchange_wait(1); ev[6].record(); dist.all_reduce(tok); ctx.local_partition_rel(1); ev[7].record(); ctx.build_probe(); ev[8].record()
+hg = rhj.hashjoin._host_barrier_group(None)
+def barrier(which):
+    if hg is not None:
+        ctx.exchange_sync(which); dist.barrier(group=hg)
+    else:
+        ctx.exchange_wait(which); dist.all_reduce(tok)
+ev[3].record(); barrier(0); ev[4].record(); ctx.local_partition_rel(0); ev[5].record()
+ev[6].record(); barrier(1); ctx.local_partition_rel(1); ev[7].record(); ctx.build_probe(); ev[8].record()
 torch.cuda.synchronize()
 names = ["hist+plan", "K2 R,S", "wait push R", "barrier R", "K3 R", "wait push S", "barrier+K3 S", "K4"]
 if rank == 0:
