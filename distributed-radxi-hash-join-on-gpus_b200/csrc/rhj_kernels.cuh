@@ -1,12 +1,19 @@
 // rhj_kernels.cuh -- the four join stages as sm_100a kernels.
 //
-//   K1  k_histogram      histograms/LocalHistogram.cpp:35-53 (and LocalPartitioning.cpp:138-163)
-//   Ks  k_colscan        per-chunk exclusive offsets (what lets the scatter write exact,
-//                        write-once positions; OffsetMap.cpp:75-85 does this per rank only)
-//   Kp  k_plan_network   GlobalHistogram.cpp:31-48, AssignmentMap.cpp:34-49, OffsetMap.cpp:59-93
-//   K2/K3 k_scatter      NetworkPartitioning.cpp:116-173 / LocalPartitioning.cpp:194-250
-//   Kq  k_plan_local     LocalPartitioning.cpp:165-192 (8-tuple padded prefix) + work list
-//   K4  k_build_probe    BuildProbe.cpp:47-121
+//   K1  k_histogram_tiles  histograms/LocalHistogram.cpp:35-53 (and LocalPartitioning.cpp:138-163);
+//                          also writes, per 8192-tuple tile, each tuple's rank inside its bin
+//                          and the bins' start slots, so the scatter needs no counting pass
+//   Ks  k_colscan          per-chunk exclusive offsets (what lets the scatter write exact,
+//                          write-once positions; OffsetMap.cpp:75-85 does this per rank only)
+//   Kp  k_plan_network     GlobalHistogram.cpp:31-48, AssignmentMap.cpp:34-49, OffsetMap.cpp:59-93
+//   K2/K3 k_scatter3       NetworkPartitioning.cpp:116-173 / LocalPartitioning.cpp:194-250
+//   Kx  k_push             the staged exchange: contiguous per-destination runs -> peer windows
+//                          (data/Window.cpp:108-115, MPI_Put)
+//   Kq  k_plan_local/items LocalPartitioning.cpp:165-192 (8-tuple padded prefix) + work list
+//   K4  k_build_probe3     BuildProbe.cpp:47-121
+//   k_histogram, k_scatter, k_build_probe are the first-generation kernels, kept selectable
+//   (RHJ_SCATTER=legacy, RHJ_BP=legacy) as the ablation baseline; k_histogram also serves the
+//   allocation-free entry point.
 //
 // All stages are HBM-bound integer work (no tensor cores).  Work is cut into
 // fixed-size chunks of consecutive tuples; the histogram and the scatter of a pass

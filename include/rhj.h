@@ -166,8 +166,8 @@ int rhj_local_partition(rhj_ctx *ctx, void *stream);
  * peers' windows are complete (MPI_Win_flush_local_all, data/Window.cpp:193-201); the barrier
  * that follows (operators/HashJoin.cpp:119-121) then means every rank's are. */
 int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream);
-/* Host-blocking form of rhj_exchange_wait, for launchers whose barrier is a host-side one (an
- * NCCL barrier issued while the other relation saturates NVLink queues behind that traffic). */
+/* Host-blocking form of rhj_exchange_wait, for launchers whose barrier is a host-side one
+ * (MPI_Barrier, gloo). */
 int rhj_exchange_sync(rhj_ctx *ctx, int which);
 int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream);
 /* tasks/LocalPartitioning.cpp:138-192 results for owned partition `p` (host copies). */
