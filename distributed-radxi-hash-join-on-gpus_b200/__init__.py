@@ -107,6 +107,7 @@ SYMBOLS = {
     "rhj_get_local_partition": (_int, [_vp, _int, _u32, _vp, _vp, _vp]),
     "rhj_get_partition_dev": (_int, [_vp, _int, _u32, _int, C.POINTER(_vp), C.POINTER(_u64)]),
     "rhj_build_probe": (_int, [_vp, _vp]),
+    "rhj_build_probe_pairs": (_int, [_vp, _vp, _u64, _vp]),
     "rhj_get_result": (_int, [_vp, _resp, _vp]),
     "rhj_get_timings": (_int, [_vp, C.POINTER(Timings)]),
     "rhj_join": (_int, [_vp, _vp, _u64, _vp, _u64, _vp, _resp]),
@@ -259,6 +260,14 @@ class Context:
 
     def build_probe(self):
         check(lib().rhj_build_probe(self.h, _stream()))
+
+    def build_probe_pairs(self, pairs, capacity: int | None = None):
+        """Build/probe with materialised output: `pairs` is a device int64 tensor with room for
+        2 * capacity values, filled with (rid_R, rid_S) rows in unspecified order."""
+        cap = capacity if capacity is not None else pairs.numel() // 2
+        if pairs.numel() < 2 * cap:
+            raise ValueError("pairs tensor is smaller than 2 * capacity")
+        check(lib().rhj_build_probe_pairs(self.h, pairs.data_ptr(), cap, _stream()))
 
     def result(self) -> Result:
         r = Result()

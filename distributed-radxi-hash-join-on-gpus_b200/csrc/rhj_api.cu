@@ -318,7 +318,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   for (int i = 0; i < 4; ++i) add(2 * NS * 8);     // sub_tot, sub_off, sub_prefix, sub_addr
   add(2 * NS * 4);                                 // sub_cnt
   add(NS * 8); add((uint64_t)nowned * 8); add(((uint64_t)nowned + 1) * 8);  // item_lstart, jcount, jstart
-  add(8); add(5 * 8); add(4);                      // work counter, result, status
+  add(16); add(5 * 8); add(4);                     // work counter + pair cursor, result, status
   add((NS + kItemSlack) * sizeof(ItemDesc));       // expanded build/probe work list
   if (nranks > 1) {                                // send buffers + push lists of the staged exchange
     add(max_local[0] * 8); add(max_local[1] * 8);
@@ -405,7 +405,7 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (!rc) rc = carve(ctx, NS, &ctx->d_item_lstart);
   if (!rc) rc = carve(ctx, (uint64_t)nowned, &ctx->d_item_jcount);
   if (!rc) rc = carve(ctx, (uint64_t)nowned + 1, &ctx->d_item_jstart);
-  if (!rc) rc = carve(ctx, 1ull, &ctx->d_work);
+  if (!rc) rc = carve(ctx, 2ull, &ctx->d_work);  // [0] work counter, [1] output cursor of rhj_build_probe_pairs
   if (!rc) rc = carve(ctx, 5ull, &ctx->d_result);
   if (!rc) rc = carve(ctx, 1ull, &ctx->d_status);
   ctx->items_cap = NS + kItemSlack;
@@ -785,7 +785,7 @@ extern "C" int rhj_local_partition(rhj_ctx *ctx, void *stream) {
   return rc;
 }
 
-template <int CAP>
+template <int CAP, bool EMIT>
 static int launch_build_probe(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_t st) {
   // the pipelined kernel relies on the 8-tuple alignment/padding of the local pass; single-pass
   // mode (arbitrary partition offsets) and wide rids use the generic kernel
@@ -803,38 +803,53 @@ static int launch_build_probe(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_
       return RHJ_OK;
     };
     int rc;
-    if (ctx->tune_bp_tpb == 512) rc = ks32 ? launch(k_build_probe3<CAP, 512, true>, 512) : launch(k_build_probe3<CAP, 512, false>, 512);
-    else rc = ks32 ? launch(k_build_probe3<CAP, 1024, true>, 1024) : launch(k_build_probe3<CAP, 1024, false>, 1024);
+    if (ctx->tune_bp_tpb == 512) rc = ks32 ? launch(k_build_probe3<CAP, 512, true, EMIT>, 512) : launch(k_build_probe3<CAP, 512, false, EMIT>, 512);
+    else rc = ks32 ? launch(k_build_probe3<CAP, 1024, true, EMIT>, 1024) : launch(k_build_probe3<CAP, 1024, false, EMIT>, 1024);
     if (rc) return rc;
     RHJ_CHECK_LAUNCH("k_build_probe3");
     // items beyond the expanded list (extreme skew) are left to the generic kernel below
     BuildProbeArgs rest = a;
     rest.item_begin = ctx->items_cap;
     size_t smem_g = build_probe_smem_bytes<CAP>();
-    RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
-    k_build_probe<CAP><<<ctx->sm_count, kBpTPB, smem_g, st>>>(rest);
+    RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP, EMIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
+    k_build_probe<CAP, EMIT><<<ctx->sm_count, kBpTPB, smem_g, st>>>(rest);
     RHJ_CHECK_LAUNCH("k_build_probe(overflow)");
     return RHJ_OK;
   }
   size_t smem = build_probe_smem_bytes<CAP>();
-  RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RHJ_CUDA(cudaFuncSetAttribute(k_build_probe<CAP, EMIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_build_probe<CAP>, kBpTPB, smem));
+  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_build_probe<CAP, EMIT>, kBpTPB, smem));
   if (per_sm < 1) per_sm = 1;
-  k_build_probe<CAP><<<ctx->sm_count * per_sm, kBpTPB, smem, st>>>(a);
+  k_build_probe<CAP, EMIT><<<ctx->sm_count * per_sm, kBpTPB, smem, st>>>(a);
   RHJ_CHECK_LAUNCH("k_build_probe");
   return RHJ_OK;
 }
 
-extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) {
+template <bool EMIT>
+static int launch_build_probe_cap(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStream_t st) {
+  switch (ctx->cap_r) {
+    case 1024: return launch_build_probe<1024, EMIT>(ctx, a, st);
+    case 2048: return launch_build_probe<2048, EMIT>(ctx, a, st);
+    case 8192: return launch_build_probe<8192, EMIT>(ctx, a, st);
+    default: return launch_build_probe<4096, EMIT>(ctx, a, st);
+  }
+}
+
+static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, bool emit, void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
+  if (emit && pairs_cap > 0 && !pairs_dev) return fail(RHJ_ERR_INVALID, "pairs_dev is NULL");
+  if (emit && (reinterpret_cast<uintptr_t>(pairs_dev) & 15)) return fail(RHJ_ERR_INVALID, "pairs_dev must be 16-byte aligned");
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (!ctx->local_planned) {
     int rc = launch_plan_local(ctx, 0, 2, true, st);
     if (rc) return rc;
   }
+  // the stage may be repeated on the same partitions (count first, then materialise)
+  RHJ_CUDA(cudaMemsetAsync(ctx->d_result, 0, 5 * 8, st));
+  RHJ_CUDA(cudaMemsetAsync(ctx->d_work, 0, 2 * 8, st));
   if (ctx->nowned > 0) {
     BuildProbeArgs a{};
     for (int k = 0; k < 2; ++k) a.src[k] = ctx->cfg.enable_two_level ? ctx->localout[k] : ctx->window[k];
@@ -856,19 +871,22 @@ extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) {
     a.status = ctx->d_status;
     a.items = ctx->d_items;
     a.items_cap = ctx->items_cap;
-    int rc;
-    switch (ctx->cap_r) {
-      case 1024: rc = launch_build_probe<1024>(ctx, a, st); break;
-      case 2048: rc = launch_build_probe<2048>(ctx, a, st); break;
-      case 8192: rc = launch_build_probe<8192>(ctx, a, st); break;
-      default: rc = launch_build_probe<4096>(ctx, a, st); break;
-    }
+    a.pairs = static_cast<ulonglong2 *>(pairs_dev);
+    a.pairs_cap = pairs_cap;
+    a.pair_cursor = ctx->d_work + 1;
+    int rc = emit ? launch_build_probe_cap<true>(ctx, a, st) : launch_build_probe_cap<false>(ctx, a, st);
     if (rc) return rc;
   }
   int rc = record(ctx, EV_BP, st);
   if (rc) return rc;
   ctx->stage = 5;
   return RHJ_OK;
+}
+
+extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) { return build_probe_impl(ctx, nullptr, 0, false, stream); }
+
+extern "C" int rhj_build_probe_pairs(rhj_ctx *ctx, rhj_pair *pairs_dev, uint64_t capacity, void *stream) {
+  return build_probe_impl(ctx, pairs_dev, capacity, true, stream);
 }
 
 // -----------------------------------------------------------------------------------

@@ -21,6 +21,8 @@
 // exact output offset for the scatter and every output slot is written once.
 #pragma once
 
+#include <cooperative_groups.h>
+
 #include "rhj_device.cuh"
 
 namespace rhj {
@@ -884,6 +886,11 @@ struct BuildProbeArgs {
   const struct ItemDesc *items;  // [items_cap] expanded work list (k_expand_items)
   uint64_t items_cap;
   uint64_t item_begin;  // generic kernel: first item it is responsible for
+  // materialised output (EMIT variants): matches append (rid_R, rid_S) at a position reserved
+  // from `pair_cursor`; pairs at positions >= pairs_cap are counted but not stored
+  ulonglong2 *pairs;
+  uint64_t pairs_cap;
+  unsigned long long *pair_cursor;
 };
 
 // One build/probe work item, fully resolved: what a CTA needs to start its loads.
@@ -944,7 +951,19 @@ __host__ __device__ constexpr size_t build_probe_smem_bytes() {
   return (size_t)CAP * (8 + 4 + 2);
 }
 
-template <int CAP>
+// EMIT: each match also reserves one output slot.  Lanes that find a match in the same step
+// share one reservation (one atomic per converged group), which is enough for the paths this
+// kernel serves: single-pass mode and work items beyond the expanded list.
+__device__ __forceinline__ void emit_pair_grouped(const BuildProbeArgs &a, uint64_t rid_r, uint64_t rid_s) {
+  const cooperative_groups::coalesced_group g = cooperative_groups::coalesced_threads();
+  unsigned long long base = 0;
+  if (g.thread_rank() == 0) base = atomicAdd(a.pair_cursor, (unsigned long long)g.size());
+  base = g.shfl(base, 0);
+  const uint64_t pos = base + g.thread_rank();
+  if (pos < a.pairs_cap) a.pairs[pos] = make_ulonglong2(rid_r, rid_s);
+}
+
+template <int CAP, bool EMIT = false>
 __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
   extern __shared__ __align__(128) unsigned char sh_raw[];
   __shared__ unsigned long long s_item;
@@ -1026,6 +1045,7 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
             acc_rr += rid_r;
             acc_rs += rid_s;
             acc_mix += mix_triple(key, rid_r, rid_s);
+            if (EMIT) emit_pair_grouped(a, rid_r, rid_s);
           }
           hit = next[hit - 1];
         }
@@ -1087,11 +1107,13 @@ __host__ __device__ constexpr size_t build_probe3_smem_bytes() {
   return (size_t)CAP * (8 + 8 + 4 + 2) + 64;
 }
 
-template <int CAP, int TPB, bool KS32>
+template <int CAP, int TPB, bool KS32, bool EMIT = false>
 __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(const BuildProbeArgs a) {
   constexpr int BATCH = TPB * kBp3SV * 2;  // probe tuples per batch
   extern __shared__ __align__(128) unsigned char sh_raw[];
   __shared__ unsigned long long s_red[5][TPB / 32];
+  __shared__ uint32_t s_wtot[EMIT ? 32 : 1];             // EMIT: matches per warp in this batch
+  __shared__ unsigned long long s_wbase[EMIT ? 32 : 1];  //       first output slot of the warp
   if (*a.status != kDevOk) return;
   uint64_t *const tup0 = reinterpret_cast<uint64_t *>(sh_raw);
   uint32_t *const bucket = reinterpret_cast<uint32_t *>(tup0 + 2 * CAP);
@@ -1200,7 +1222,7 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
         }
       }
     };
-    {
+    if constexpr (!EMIT) {
       const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(a.src[1] + c_lo.y) + tid;
       for (uint32_t base = 0; base < s_n; base += BATCH) {
         if (base > 0) {
@@ -1213,6 +1235,99 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
           const uint32_t e = base + 2 * (u * TPB + tid);
           if (e < s_n) probe(xs_cur[u].x);
           if (e + 1 < s_n) probe(xs_cur[u].y);
+        }
+      }
+    } else {
+      // Materialising probe.  Per batch: (1) probe as above, remembering per probe tuple how
+      // many matches it has and its first one; (2) one output range per CTA is reserved with a
+      // single atomic and cut up by a scan -- inside a warp in tuple-major order, so that the
+      // lanes of one store instruction write neighbouring 16-byte pairs; (3) the pairs are
+      // written; only tuples with more than one match walk their chain a second time.
+      constexpr int NQ = 2 * kBp3SV;
+      const uint32_t lane = tid & 31, warp = tid >> 5;
+      const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(a.src[1] + c_lo.y) + tid;
+      for (uint32_t base = 0; base < s_n; base += BATCH) {
+        if (base > 0) {
+#pragma unroll
+          for (int u = 0; u < kBp3SV; ++u)
+            if (base + 2 * (u * TPB + tid) < s_n) xs_cur[u] = ld_stream_v2(v2 + base / 2 + u * TPB);
+        }
+        uint32_t m[NQ], first[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          const uint32_t e = base + 2 * ((q >> 1) * TPB + tid) + (q & 1);
+          const uint64_t v = (q & 1) ? xs_cur[q >> 1].y : xs_cur[q >> 1].x;
+          m[q] = 0;
+          first[q] = 0;
+          if (e < s_n) {
+            const uint64_t kpart = v >> a.key_shift;
+            uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
+            while (hit) {
+              const uint64_t r = t[hit - 1];
+              if ((r >> a.key_shift) == kpart) {
+                const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
+                if (m[q] == 0) first[q] = hit;
+                m[q] += 1;
+                item_n += 1;
+                item_kpart += kpart;
+                acc_rr += rid_r;
+                acc_rs += rid_s;
+                acc_mix += mix_triple((kpart << a.net_bits) | partition, rid_r, rid_s);
+              }
+              hit = next[hit - 1];
+            }
+          }
+        }
+        uint32_t off[NQ], wtot = 0;
+        uint32_t mmax = 0;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) mmax = max(mmax, m[q]);
+        if (!__any_sync(0xFFFFFFFFu, mmax > 1)) {  // unique build keys: one vote per tuple slot
+#pragma unroll
+          for (int q = 0; q < NQ; ++q) {
+            const uint32_t b = __ballot_sync(0xFFFFFFFFu, m[q] != 0);
+            off[q] = wtot + __popc(b & ((1u << lane) - 1));
+            wtot += __popc(b);
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < NQ; ++q) {
+            const uint32_t incl = warp_inclusive_scan(m[q]);
+            off[q] = wtot + incl - m[q];
+            wtot += __shfl_sync(0xFFFFFFFFu, incl, 31);
+          }
+        }
+        if (lane == 0) s_wtot[warp] = wtot;
+        __syncthreads();
+        if (warp == 0) {
+          const uint32_t x = lane < TPB / 32 ? s_wtot[lane] : 0;
+          const uint32_t incl = warp_inclusive_scan(x);
+          const uint32_t cta_total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+          unsigned long long gb = 0;
+          if (lane == 0 && cta_total) gb = atomicAdd(a.pair_cursor, (unsigned long long)cta_total);
+          gb = __shfl_sync(0xFFFFFFFFu, gb, 0);
+          s_wbase[lane] = gb + incl - x;
+        }
+        __syncthreads();
+        const uint64_t wb = s_wbase[warp];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          if (m[q] == 0) continue;
+          const uint64_t v = (q & 1) ? xs_cur[q >> 1].y : xs_cur[q >> 1].x;
+          const uint64_t rid_s = v & rid_mask;
+          uint64_t pos = wb + off[q];
+          if (m[q] == 1) {
+            if (pos < a.pairs_cap) a.pairs[pos] = make_ulonglong2(t[first[q] - 1] & rid_mask, rid_s);
+          } else {
+            const uint64_t kpart = v >> a.key_shift;
+            for (uint32_t hit = first[q]; hit; hit = next[hit - 1]) {
+              const uint64_t r = t[hit - 1];
+              if ((r >> a.key_shift) == kpart) {
+                if (pos < a.pairs_cap) a.pairs[pos] = make_ulonglong2(r & rid_mask, rid_s);
+                ++pos;
+              }
+            }
+          }
         }
       }
     }

@@ -198,10 +198,11 @@ RHJ_GETTER(getOuterRelationWriteOffsets, rhj_get_write_offsets, 1)
 
 void LocalPartitioning::execute() {
   check(rhj_local_partition(ctx, stream));
-  operators::HashJoin::TASK_QUEUE.push(new BuildProbe(ctx, stream));
+  operators::HashJoin::TASK_QUEUE.push(new BuildProbe(ctx, stream, pairs, capacity));
 }
 void BuildProbe::execute() {
-  check(rhj_build_probe(ctx, stream));
+  if (pairs) check(rhj_build_probe_pairs(ctx, pairs, capacity, stream));
+  else check(rhj_build_probe(ctx, stream));
   rhj_result r;
   check(rhj_get_result(ctx, &r, stream));
   operators::HashJoin::RESULT_COUNTER += r.matches;
@@ -216,12 +217,14 @@ void BuildProbe::execute() {
 namespace operators {
 uint64_t HashJoin::RESULT_COUNTER = 0;
 uint64_t HashJoin::RESULT_CHECKSUM[4] = {0, 0, 0, 0};
+uint64_t HashJoin::RESULT_PAIR_CAPACITY = 0;
 std::queue<tasks::Task *> HashJoin::TASK_QUEUE;
 
 HashJoin::HashJoin(uint32_t numberOfNodes, uint32_t nodeId, data::Relation *innerRelation,
                    data::Relation *outerRelation, data::Comm *comm_, int device)
     : numberOfNodes(numberOfNodes), nodeId(nodeId), innerRelation(innerRelation), outerRelation(outerRelation),
-      comm(comm_ ? comm_ : &single), ctx(nullptr), dInner(nullptr), dOuter(nullptr), stream(nullptr) {
+      comm(comm_ ? comm_ : &single), ctx(nullptr), dInner(nullptr), dOuter(nullptr), dPairs(nullptr), pairsThisJoin(0),
+      stream(nullptr) {
   rhj_config cfg = core::Configuration::toConfig();
   check(rhj_init(&ctx, (int)nodeId, (int)numberOfNodes, device, &cfg));
   memory::Pool::bind(ctx);
@@ -232,9 +235,11 @@ HashJoin::HashJoin(uint32_t numberOfNodes, uint32_t nodeId, data::Relation *inne
   const uint64_t wi = (uint64_t)(core::Configuration::ALLOCATION_FACTOR * (double)innerRelation->getGlobalSize() / numberOfNodes) + 1024;
   const uint64_t wo = (uint64_t)(core::Configuration::ALLOCATION_FACTOR * (double)outerRelation->getGlobalSize() / numberOfNodes) + 1024;
   memory::Pool::allocate(inputs + rhj_workspace_bytes(&cfg, (int)numberOfNodes, ni, no, wi, wo) +
-                         (uint64_t)numberOfNodes * 4 * core::Configuration::NETWORK_PARTITIONING_COUNT() * 8 + 4096);
+                         (uint64_t)numberOfNodes * 4 * core::Configuration::NETWORK_PARTITIONING_COUNT() * 8 + 4096 +
+                         RESULT_PAIR_CAPACITY * sizeof(rhj_pair) + 4096);
   dInner = memory::Pool::getMemory(ni * sizeof(data::Tuple));
   dOuter = memory::Pool::getMemory(no * sizeof(data::Tuple));
+  if (RESULT_PAIR_CAPACITY) dPairs = static_cast<rhj_pair *>(memory::Pool::getMemory(RESULT_PAIR_CAPACITY * sizeof(rhj_pair)));
   check(rhj_memcpy_h2d(dInner, innerRelation->getData(), ni * sizeof(data::Tuple)));
   check(rhj_memcpy_h2d(dOuter, outerRelation->getData(), no * sizeof(data::Tuple)));
   check(rhj_plan(ctx, ni, no, wi, wo));
@@ -268,8 +273,9 @@ void HashJoin::join() {
 
   comm->barrier(stream);  // operators/HashJoin.cpp:119-121: every put has landed
 
-  if (core::Configuration::ENABLE_TWO_LEVEL_PARTITIONING) TASK_QUEUE.push(new tasks::LocalPartitioning(ctx, stream));
-  else TASK_QUEUE.push(new tasks::LocalPartitioning(ctx, stream));  // no-op pass, then BuildProbe (HashJoin.cpp:151-156)
+  // two-level off: the pass is a no-op and only queues BuildProbe (HashJoin.cpp:151-156)
+  const uint64_t before = RESULT_COUNTER;
+  TASK_QUEUE.push(new tasks::LocalPartitioning(ctx, stream, dPairs, dPairs ? RESULT_PAIR_CAPACITY : 0));
 
   while (!TASK_QUEUE.empty()) {  // operators/HashJoin.cpp:187-204
     tasks::Task *task = TASK_QUEUE.front();
@@ -278,6 +284,14 @@ void HashJoin::join() {
     delete task;
   }
   performance::Measurements::stopJoin(ctx);
+  pairsThisJoin = RESULT_COUNTER - before;
+}
+
+std::vector<rhj_pair> HashJoin::getResultPairs() {
+  const uint64_t n = dPairs ? (pairsThisJoin < RESULT_PAIR_CAPACITY ? pairsThisJoin : RESULT_PAIR_CAPACITY) : 0;
+  std::vector<rhj_pair> out(n);
+  if (n) check(rhj_memcpy_d2h(out.data(), dPairs, n * sizeof(rhj_pair)));
+  return out;
 }
 }  // namespace operators
 

@@ -143,6 +143,12 @@ class HashJoin {  // operators/HashJoin.h:23-43
   ~HashJoin();
   void join();
   rhj_ctx *context() { return ctx; }
+  // Materialised output (no counterpart in the reference, which only counts): set
+  // RESULT_PAIR_CAPACITY before constructing the operator and join() also writes up to that many
+  // (rid_R, rid_S) pairs of this rank to device memory; getResultPairs copies them to the host.
+  static uint64_t RESULT_PAIR_CAPACITY;
+  rhj_pair *resultPairsDevice() { return dPairs; }
+  std::vector<rhj_pair> getResultPairs();
 
   static uint64_t RESULT_COUNTER;                       // operators/HashJoin.cpp:28
   static uint64_t RESULT_CHECKSUM[4];                   // sum key, sum rid_R, sum rid_S, sum mix (this project's addition)
@@ -155,6 +161,8 @@ class HashJoin {  // operators/HashJoin.h:23-43
   data::SingleRank single;
   rhj_ctx *ctx;
   void *dInner, *dOuter;  // device copies of the relations (pool memory)
+  rhj_pair *dPairs;       // pool memory, RESULT_PAIR_CAPACITY entries (nullptr: count only)
+  uint64_t pairsThisJoin;
   void *stream;
 };
 }  // namespace operators
@@ -192,21 +200,27 @@ class NetworkPartitioning : public Task {
 };
 class LocalPartitioning : public Task {
  public:
-  LocalPartitioning(rhj_ctx *ctx, void *stream) : ctx(ctx), stream(stream) {}
+  LocalPartitioning(rhj_ctx *ctx, void *stream, rhj_pair *pairs = nullptr, uint64_t capacity = 0)
+      : ctx(ctx), stream(stream), pairs(pairs), capacity(capacity) {}
   void execute() override;  // also queues the BuildProbe task, as tasks/LocalPartitioning.cpp:116-124 does
   task_type_t getType() override { return TASK_PARTITION; }
  private:
   rhj_ctx *ctx;
   void *stream;
+  rhj_pair *pairs;
+  uint64_t capacity;
 };
 class BuildProbe : public Task {
  public:
-  BuildProbe(rhj_ctx *ctx, void *stream) : ctx(ctx), stream(stream) {}
+  BuildProbe(rhj_ctx *ctx, void *stream, rhj_pair *pairs = nullptr, uint64_t capacity = 0)
+      : ctx(ctx), stream(stream), pairs(pairs), capacity(capacity) {}
   void execute() override;  // adds this rank's matches to HashJoin::RESULT_COUNTER (tasks/BuildProbe.cpp:115)
   task_type_t getType() override { return TASK_BUILD_PROBE; }
  private:
   rhj_ctx *ctx;
   void *stream;
+  rhj_pair *pairs;
+  uint64_t capacity;
 };
 }  // namespace tasks
 

@@ -67,6 +67,12 @@ typedef struct rhj_result {
   uint64_t sum_mix;
 } rhj_result;
 
+/* One materialised match: the record ids of the build-side and the probe-side tuple. */
+typedef struct rhj_pair {
+  uint64_t rid_r;
+  uint64_t rid_s;
+} rhj_pair;
+
 /* Device timings of the last join, microseconds, under the reference's own keys
  * (performance/Measurements.cpp:136-142, 246-268). */
 typedef struct rhj_timings {
@@ -180,6 +186,15 @@ int rhj_get_partition_dev(rhj_ctx *ctx, int which, uint32_t p, int after_local_p
 
 /* TASK_BUILD_PROBE -- tasks/BuildProbe.cpp:47-121 for every (sub-)partition pair this rank owns. */
 int rhj_build_probe(rhj_ctx *ctx, void *stream);
+/* The same stage with its output materialised: where the reference's probe loop
+ * does `++matches` (tasks/BuildProbe.cpp:101-104; the unbuilt GPU probe kernels write pairs,
+ * operators/gpu/kernels.cu:237-241), every match also appends one rhj_pair to `pairs_dev`
+ * (device memory of this rank, 16-byte aligned, room for `capacity` pairs).  The order of the
+ * pairs is unspecified.  rhj_get_result reports the full count and checksum as after
+ * rhj_build_probe; min(matches, capacity) pairs have been written, the rest are only counted.
+ * Either build/probe entry point may be called again on the same partitions (count first, size
+ * the buffer, then materialise). */
+int rhj_build_probe_pairs(rhj_ctx *ctx, rhj_pair *pairs_dev, uint64_t capacity, void *stream);
 
 /* Result of this rank (HashJoin::RESULT_COUNTER + checksum); synchronises `stream`
  * and reports device-side capacity errors. */

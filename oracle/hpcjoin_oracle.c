@@ -322,8 +322,10 @@ static uint64_t next_pow2_ref(uint64_t v) {
  * a probe tuple matches when value>>keyShift is equal (:101-102), every
  * duplicate counts.  `partition` (not known to the reference task) restores
  * the key's low bits for the checksum. */
-void orc_build_probe(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t ns,
-                     const orc_config *cfg, uint32_t partition, orc_result *acc) {
+/* tasks/BuildProbe.cpp:47-121.  The reference only counts (`:97-106`); with a sink, every match
+ * additionally appends (rid_R, rid_S) -- the materialised operator output. */
+void orc_build_probe_pairs(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t ns,
+                           const orc_config *cfg, uint32_t partition, orc_result *acc, orc_pair_sink *sink) {
   if (nr == 0 || ns == 0) return;
   uint32_t key_shift = cfg->net_bits + cfg->payload_bits;
   uint32_t shift_bits = key_shift + cfg->loc_bits;
@@ -350,6 +352,13 @@ void orc_build_probe(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t
         acc->sum_rid_r += rid_r;
         acc->sum_rid_s += rid_s;
         acc->sum_mix += orc_mix(key, rid_r, rid_s);
+        if (sink) {
+          if (sink->n < sink->cap) {
+            sink->pairs[2 * sink->n] = rid_r;
+            sink->pairs[2 * sink->n + 1] = rid_s;
+          }
+          sink->n += 1;
+        }
       }
     }
   }
@@ -357,15 +366,20 @@ void orc_build_probe(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t
   free(bucket);
 }
 
+void orc_build_probe(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t ns,
+                     const orc_config *cfg, uint32_t partition, orc_result *acc) {
+  orc_build_probe_pairs(r, nr, s, ns, cfg, partition, acc, NULL);
+}
+
 /* ------------------------------------------------------------------------ */
 /* operators/HashJoin.cpp:45-220 for all ranks, simulated in one process        */
 /* ------------------------------------------------------------------------ */
 
 static void join_partition(const uint64_t *rp, uint64_t nr, const uint64_t *sp, uint64_t ns,
-                           const orc_config *cfg, uint32_t p, orc_result *acc) {
+                           const orc_config *cfg, uint32_t p, orc_result *acc, orc_pair_sink *sink) {
   if (!cfg->two_level) {
     /* HashJoin.cpp:151-156: one BuildProbe per owned network partition */
-    orc_build_probe(rp, nr, sp, ns, cfg, p, acc);
+    orc_build_probe_pairs(rp, nr, sp, ns, cfg, p, acc, sink);
     return;
   }
   /* tasks/LocalPartitioning.cpp:59-136 */
@@ -381,12 +395,18 @@ static void join_partition(const uint64_t *rp, uint64_t nr, const uint64_t *sp, 
   orc_local_part_scatter(rp, nr, cfg, pr, ro);
   orc_local_part_scatter(sp, ns, cfg, ps, so);
   for (uint32_t q = 0; q < sub; ++q)
-    if (hr[q] > 0 && hs[q] > 0) orc_build_probe(ro + pr[q], hr[q], so + ps[q], hs[q], cfg, p, acc);
+    if (hr[q] > 0 && hs[q] > 0) orc_build_probe_pairs(ro + pr[q], hr[q], so + ps[q], hs[q], cfg, p, acc, sink);
   free(hr); free(hs); free(pr); free(ps); free(ro); free(so);
 }
 
 int orc_join(const orc_tuple *const *inner, const uint64_t *inner_n, const orc_tuple *const *outer,
              const uint64_t *outer_n, uint32_t nranks, const orc_config *cfg, orc_result *per_rank) {
+  return orc_join_pairs(inner, inner_n, outer, outer_n, nranks, cfg, per_rank, NULL);
+}
+
+int orc_join_pairs(const orc_tuple *const *inner, const uint64_t *inner_n, const orc_tuple *const *outer,
+                   const uint64_t *outer_n, uint32_t nranks, const orc_config *cfg, orc_result *per_rank,
+                   orc_pair_sink *sinks) {
   uint32_t parts = 1u << cfg->net_bits;
   uint64_t *loc[2], *glob[2];
   uint32_t *assign = (uint32_t *)malloc(parts * sizeof(uint32_t));
@@ -422,7 +442,7 @@ int orc_join(const orc_tuple *const *inner, const uint64_t *inner_n, const orc_t
     for (uint32_t p = 0; p < parts; ++p) {
       if (assign[p] != r) continue;
       join_partition(win[0][r] + base[0][p], glob[0][p], win[1][r] + base[1][p], glob[1][p], cfg, p,
-                     &per_rank[r]);
+                     &per_rank[r], sinks ? &sinks[r] : NULL);
     }
   }
   for (int k = 0; k < 2; ++k) {

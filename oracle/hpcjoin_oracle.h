@@ -99,9 +99,24 @@ uint64_t orc_mix(uint64_t key, uint64_t rid_r, uint64_t rid_s);
 void orc_build_probe(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t ns,
                      const orc_config *cfg, uint32_t partition, orc_result *acc);
 
+/* Materialised output: the reference's probe loop with `++matches`
+ * (tasks/BuildProbe.cpp:101-104) additionally appending (rid_R, rid_S).  `pairs` holds
+ * 2*cap u64; `n` counts every match, also those beyond `cap` (which are not stored). */
+typedef struct {
+  uint64_t *pairs;
+  uint64_t cap;
+  uint64_t n;
+} orc_pair_sink;
+void orc_build_probe_pairs(const uint64_t *r, uint64_t nr, const uint64_t *s, uint64_t ns,
+                           const orc_config *cfg, uint32_t partition, orc_result *acc, orc_pair_sink *sink);
+
 /* ---- the whole operator, all ranks simulated in-process ------------------ */
 int orc_join(const orc_tuple *const *inner, const uint64_t *inner_n, const orc_tuple *const *outer,
              const uint64_t *outer_n, uint32_t nranks, const orc_config *cfg, orc_result *per_rank);
+/* orc_join with one pair sink per rank (NULL: count only). */
+int orc_join_pairs(const orc_tuple *const *inner, const uint64_t *inner_n, const orc_tuple *const *outer,
+                   const uint64_t *outer_n, uint32_t nranks, const orc_config *cfg, orc_result *per_rank,
+                   orc_pair_sink *sinks);
 /* Same pipeline starting from already-compressed 8-byte tuples (BASELINE config 5):
  * `value` must be packed as orc_compress() would, partition = low net_bits of `key`
  * supplied beside it is impossible, so input is (partition-less) raw: key in the

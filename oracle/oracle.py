@@ -93,6 +93,8 @@ def lib():
         L.orc_build_probe.argtypes = [vp, u64, vp, u64, cfgp, u32, C.POINTER(Result)]
         L.orc_join.restype = C.c_int
         L.orc_join.argtypes = [vp, vp, vp, vp, u32, cfgp, vp]
+        L.orc_join_pairs.restype = C.c_int
+        L.orc_join_pairs.argtypes = [vp, vp, vp, vp, u32, cfgp, vp, vp]
         L.orc_pack8.restype = u64
         L.orc_pack8.argtypes = [u64, u64, u32]
         L.orc_bruteforce_join.argtypes = [vp, u64, vp, u64, C.POINTER(Result)]
@@ -246,6 +248,27 @@ def join(inner: list, outer: list, cfg: Config) -> list:
     rc = lib().orc_join(ip, in_n, op, on_n, nranks, C.byref(cfg), res)
     assert rc == 0
     return list(res)
+
+
+class PairSink(C.Structure):
+    _fields_ = [("pairs", C.c_void_p), ("cap", C.c_uint64), ("n", C.c_uint64)]
+
+
+def join_pairs(inner: list, outer: list, cfg: Config, cap: int) -> tuple:
+    """orc_join with materialised output: returns (results per rank, pairs per rank) where pairs is
+    a u64 array [n, 2] of (rid_R, rid_S) in the reference's probe order (at most `cap` rows per rank)
+    and the true number of matches is results[r].matches."""
+    nranks = len(inner)
+    ip = (C.c_void_p * nranks)(*[a.ctypes.data for a in inner])
+    op = (C.c_void_p * nranks)(*[a.ctypes.data for a in outer])
+    in_n = (C.c_uint64 * nranks)(*[len(a) for a in inner])
+    on_n = (C.c_uint64 * nranks)(*[len(a) for a in outer])
+    res = (Result * nranks)()
+    bufs = [np.zeros((max(cap, 1), 2), np.uint64) for _ in range(nranks)]
+    sinks = (PairSink * nranks)(*[PairSink(b.ctypes.data, cap, 0) for b in bufs])
+    rc = lib().orc_join_pairs(ip, in_n, op, on_n, nranks, C.byref(cfg), res, sinks)
+    assert rc == 0
+    return list(res), [bufs[r][: min(sinks[r].n, cap)] for r in range(nranks)]
 
 
 def total(results) -> tuple:

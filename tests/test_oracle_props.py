@@ -75,3 +75,39 @@ def test_empty_relations(oracle):
     for a, b in ((e, e), (e, t), (t, e)):
         for tl in (0, 1):
             assert oracle.join([a], [b], oracle.Config(3, 2, 29, tl))[0].astuple() == (0, 0, 0, 0, 0)
+
+
+@pytest.mark.parametrize("two_level", [False, True])
+def test_materialised_pairs_equal_an_independent_equi_join(oracle, two_level):
+    """join_pairs (the probe loop of BuildProbe.cpp:97-106 with an append) against pairs built
+    independently with numpy from the raw tuples; 3 ranks, duplicates on both sides, misses."""
+    rng = np.random.default_rng(5)
+    inner, outer = [], []
+    for r in range(3):
+        a = np.zeros(4000, oracle.TUPLE)
+        a["key"] = rng.integers(0, 3000, len(a))
+        a["rid"] = np.arange(len(a)) + r * 10000
+        b = np.zeros(7000, oracle.TUPLE)
+        b["key"] = rng.integers(0, 5000, len(b))
+        b["rid"] = np.arange(len(b)) + 500000 + r * 10000
+        inner.append(a)
+        outer.append(b)
+    cfg = oracle.Config(3, 3, 29, two_level)
+    res, pairs = oracle.join_pairs(inner, outer, cfg, 200000)
+    R, S = np.concatenate(inner), np.concatenate(outer)
+    want = []
+    by_key = {}
+    for k, rid in zip(R["key"].tolist(), R["rid"].tolist()):
+        by_key.setdefault(k, []).append(rid)
+    for k, rid in zip(S["key"].tolist(), S["rid"].tolist()):
+        for rr in by_key.get(k, ()):
+            want.append((rr, rid))
+    got = sorted(tuple(x) for p in pairs for x in p.tolist())
+    assert got == sorted(want)
+    assert sum(r.matches for r in res) == len(want)
+    for r in range(3):  # a pair lands on the rank that owns its key's partition (AssignmentMap.cpp:41-43)
+        assert len(pairs[r]) == res[r].matches
+    # capacity smaller than the output: everything is counted, only `cap` rows are stored
+    res2, pairs2 = oracle.join_pairs(inner, outer, cfg, 10)
+    assert [r.astuple() for r in res2] == [r.astuple() for r in res]
+    assert all(len(p) == min(10, r.matches) for p, r in zip(pairs2, res2))
