@@ -71,3 +71,104 @@ def test_two_gpus_nccl_ipc(oracle, tmp_path, knobs):
         for rep in range(2):
             assert tuple(int(x) for x in got[rep]) == want[r].astuple()
         assert np.array_equal(np.load(tmp_path / f"ghist{r}.npy"), glob)
+
+
+RADIX_BITS = {2: (8, 9), 4: (9, 9), 8: (9, 10)}  # as bench.py: sub-partitions stay ~4 K tuples
+
+
+def _worker_config(rank, world, port, shape, log2n, out_dir):
+    """BASELINE configs 4 and 5 at their full per-GPU size, generated on the device (no host copy of
+    the relations exists), checked through closed forms that do not depend on the size."""
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    net, loc = RADIX_BITS[world]
+    m64 = (1 << 64) - 1
+    if shape == "c5":  # 1:16, packed 8-byte tuples, every build key matched 16 times
+        ns = 1 << log2n
+        nr = ns >> 4
+        NR, NS = nr * world, ns * world
+        cfg = rhj.make_config(net, loc - 2, 32 - net, True, tuple_bytes=8)
+        dr = torch.empty(nr, dtype=torch.int64, device=dev)
+        ds = torch.empty(ns, dtype=torch.int64, device=dev)
+        rhj.fill_perm(dr, 8, nr, rank * nr, NR, seed=31, start_rid=rank * nr)
+        rhj.fill_perm(ds, 8, ns, rank * ns, NS, seed=32, modulo=NR, start_rid=rank * ns)
+        want = (NS, 16 * (NR * (NR - 1) // 2) & m64, 16 * (NR * (NR - 1) // 2) & m64, NS * (NS - 1) // 2 & m64)
+        tb, caps = 8, (2 * nr, 2 * ns)
+    else:  # "c4": Zipf(1)-like probe keys (P(k) ~ 1/k), unique build keys covering the whole domain
+        n = 1 << log2n
+        nr = ns = n
+        NR = NS = n * world
+        cfg = rhj.make_config(net, loc, 32 - net, True)
+        dr = torch.empty(2 * n, dtype=torch.int64, device=dev)
+        ds = torch.empty(2 * n, dtype=torch.int64, device=dev)
+        rhj.fill_perm(dr, 16, n, rank * n, NR, seed=41, start_rid=rank * n)
+        g = torch.Generator(device=dev)
+        g.manual_seed(1000 + rank)
+        keys = ds.view(-1, 2)[:, 0]
+        step = 1 << 24
+        for b in range(0, n, step):
+            u = torch.rand(min(step, n - b), device=dev, dtype=torch.float64, generator=g)
+            keys[b:b + step] = torch.clamp(torch.floor(torch.exp(u * float(np.log(NR)))).to(torch.int64) - 1, 0, NR - 1)
+        ds.view(-1, 2)[:, 1] = torch.arange(rank * n, (rank + 1) * n, device=dev)
+        ksum = keys.sum().reshape(1)  # int64 wrap-around = arithmetic modulo 2^64
+        dist.all_reduce(ksum)
+        # rid_R of the partner of key k is the position of k in the permutation: not closed-form -> not compared
+        want = (NS, int(ksum.item()) & m64, None, NS * (NS - 1) // 2 & m64)
+        tb, caps = 16, (2 * n, 2 * n)
+    ri = rhj.Relation(dr, nr, NR, tb)
+    ro = rhj.Relation(ds, ns, NS, tb)
+    hj = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=rank, window_caps=caps)
+    hj.join()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dist.barrier()
+    e0.record()
+    r = hj.join()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    mine = torch.tensor([v - (1 << 64) if v >= (1 << 63) else v for v in r.astuple()[:4]], dtype=torch.int64, device=dev)
+    share = torch.tensor([r.matches], dtype=torch.int64, device=dev)
+    shares = [torch.zeros_like(share) for _ in range(world)]
+    dist.all_gather(shares, share)
+    dist.all_reduce(mine)
+    if rank == 0:
+        got = tuple(int(x) & m64 for x in mine.tolist())
+        import json
+        with open(os.path.join(out_dir, "result.json"), "w") as f:
+            json.dump({"shape": shape, "world": world, "got": got, "want": want, "ms": float(ms.item()),
+                       "tuples_per_s": (NR + NS) / float(ms.item()) * 1e3,
+                       "matches_per_rank": [int(s.item()) for s in shares]}, f)
+    dist.barrier()
+    hj.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("shape", ["c5", "c4"])
+def test_baseline_configs_4_and_5_full_size_all_gpus(tmp_path, shape):
+    """256 M probe tuples per GPU on every GPU of the box (2, 4 or 8)."""
+    import json
+    import torch
+    world = torch.cuda.device_count()
+    world = 8 if world >= 8 else 4 if world >= 4 else world
+    if world < 2:
+        pytest.skip("needs at least two GPUs")
+    import torch.multiprocessing as mp
+    mp.spawn(_worker_config, args=(world, _free_port(), shape, 28, str(tmp_path)), nprocs=world, join=True)
+    res = json.load(open(tmp_path / "result.json"))
+    print("\n[config]", json.dumps(res))
+    keep = os.environ.get("RHJ_KEEP_RESULTS")
+    if keep:
+        os.makedirs(keep, exist_ok=True)
+        json.dump(res, open(os.path.join(keep, f"config_{shape}_n{world}.json"), "w"))
+    for got, want in zip(res["got"], res["want"]):
+        if want is not None:
+            assert got == want
