@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--net-bits", type=int, default=0, help="network radix bits (0 = by GPU count)")
     ap.add_argument("--loc-bits", type=int, default=0, help="local radix bits (0 = by GPU count)")
     ap.add_argument("--agg", action="store_true", help="warp-aggregated histogram atomics")
+    ap.add_argument("--build-cap", type=int, default=0, help="build slice capacity (0 = library default)")
     return ap.parse_args()
 
 
@@ -212,7 +213,8 @@ def run_ours(args):
     default_bits = {1: (8, 8), 2: (8, 9), 4: (9, 9), 8: (9, 10)}.get(world, (9, 10))
     net_bits = args.net_bits or default_bits[0]
     loc_bits = args.loc_bits or default_bits[1]
-    cfg = rhj.make_config(net_bits, loc_bits, 32 - net_bits, True, tuple_bytes=16, chunk_tuples=args.chunk, flags=flags)
+    cfg = rhj.make_config(net_bits, loc_bits, 32 - net_bits, True, tuple_bytes=16, build_capacity=args.build_cap,
+                          chunk_tuples=args.chunk, flags=flags)
 
     # synthetic relations, generated on the device (harness generator, bit-identical to the oracle's)
     d_inner = torch.empty(2 * n, dtype=torch.int64, device=dev)

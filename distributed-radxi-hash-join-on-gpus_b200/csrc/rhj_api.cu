@@ -58,7 +58,7 @@ extern "C" const char *rhj_version(void) { return "rhj_b200 0.1 (sm_100a)"; }
 // -----------------------------------------------------------------------------------
 static constexpr int kMaxRanks = 64;
 static constexpr uint32_t kDefaultChunk = 1u << 16;
-static constexpr uint32_t kDefaultBuildCap = 4096;
+static constexpr uint32_t kDefaultBuildCap = 5120;  // 4096 + head-room: see bucket_slots()
 static constexpr uint64_t kAlign = 256;
 static constexpr uint64_t kItemSlack = 65536;  // work-list entries beyond one per sub-partition
 
@@ -145,8 +145,8 @@ static int validate_config(const rhj_config *c, int rank, int nranks) {
   if (c->allocation_factor != 0 && c->allocation_factor < 1.0)
     return fail(RHJ_ERR_INVALID, "allocation_factor must be >= 1.0");
   uint32_t cap = c->build_capacity ? c->build_capacity : kDefaultBuildCap;
-  if (cap != 1024 && cap != 2048 && cap != 4096 && cap != 8192)
-    return fail(RHJ_ERR_INVALID, "build_capacity must be 1024, 2048, 4096 or 8192");
+  if (cap != 1024 && cap != 2048 && cap != 4096 && cap != 5120 && cap != 8192)
+    return fail(RHJ_ERR_INVALID, "build_capacity must be 1024, 2048, 4096, 5120 or 8192");
   uint32_t chunk = c->chunk_tuples ? c->chunk_tuples : kDefaultChunk;
   if (chunk % kTile != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kTile);
   return RHJ_OK;
@@ -831,6 +831,7 @@ static int launch_build_probe_cap(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStr
   switch (ctx->cap_r) {
     case 1024: return launch_build_probe<1024, EMIT>(ctx, a, st);
     case 2048: return launch_build_probe<2048, EMIT>(ctx, a, st);
+    case 5120: return launch_build_probe<5120, EMIT>(ctx, a, st);
     case 8192: return launch_build_probe<8192, EMIT>(ctx, a, st);
     default: return launch_build_probe<4096, EMIT>(ctx, a, st);
   }

@@ -946,9 +946,20 @@ __global__ void __launch_bounds__(256) k_expand_items(BuildProbeArgs a, ItemDesc
     }
 }
 
+// Bucket heads of the shared-memory table: the largest power of two <= CAP.  A build slice of up
+// to CAP tuples hashes into min(nextpow2(slice), bucket_slots) chains, so a capacity such as 5120
+// keeps sub-partitions that come out a little above 4096 tuples in one work item (load factor <=
+// 1.25) instead of splitting them and probing their S side twice.
+template <int CAP>
+__host__ __device__ constexpr uint32_t bucket_slots() {
+  uint32_t n = 1;
+  while (n * 2 <= (uint32_t)CAP) n *= 2;
+  return n;
+}
+
 template <int CAP>
 __host__ __device__ constexpr size_t build_probe_smem_bytes() {
-  return (size_t)CAP * (8 + 4 + 2);
+  return (size_t)CAP * (8 + 2) + (size_t)bucket_slots<CAP>() * 4;
 }
 
 // EMIT: each match also reserves one output slot.  Lanes that find a match in the same step
@@ -971,7 +982,7 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
   if (*a.status != kDevOk) return;
   uint64_t *tup = reinterpret_cast<uint64_t *>(sh_raw);
   uint32_t *bucket = reinterpret_cast<uint32_t *>(tup + CAP);
-  uint16_t *next = reinterpret_cast<uint16_t *>(bucket + CAP);
+  uint16_t *next = reinterpret_cast<uint16_t *>(bucket + bucket_slots<CAP>());
   const uint32_t tid = threadIdx.x;
   const uint64_t rid_mask = a.key_shift >= 64 ? ~0ull : ((1ull << a.key_shift) - 1);
   const uint64_t total_items = a.item_jstart[a.nowned];
@@ -996,7 +1007,7 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
 
     // table size: next power of two of the slice (BuildProbe.cpp:59-60 uses the partition size)
     uint32_t nb = 1;
-    while (nb < r_n) nb <<= 1;
+    while (nb < r_n && nb < bucket_slots<CAP>()) nb <<= 1;
     const uint32_t hmask = nb - 1;
     for (uint32_t i = tid; i < nb; i += kBpTPB) bucket[i] = 0;
     __syncthreads();
@@ -1104,7 +1115,7 @@ constexpr int kBp3SV = 2;  // 16-byte probe vectors per thread per batch
 
 template <int CAP>
 __host__ __device__ constexpr size_t build_probe3_smem_bytes() {
-  return (size_t)CAP * (8 + 8 + 4 + 2) + 64;
+  return (size_t)CAP * (8 + 8 + 2) + (size_t)bucket_slots<CAP>() * 4 + 64;
 }
 
 template <int CAP, int TPB, bool KS32, bool EMIT = false>
@@ -1117,8 +1128,9 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
   if (*a.status != kDevOk) return;
   uint64_t *const tup0 = reinterpret_cast<uint64_t *>(sh_raw);
   uint32_t *const bucket = reinterpret_cast<uint32_t *>(tup0 + 2 * CAP);
-  uint16_t *const next = reinterpret_cast<uint16_t *>(bucket + CAP);
+  uint16_t *const next = reinterpret_cast<uint16_t *>(bucket + bucket_slots<CAP>());
   uint64_t *const bars = reinterpret_cast<uint64_t *>(next + CAP);
+  static_assert(CAP % 4 == 0, "mbarriers behind next[] must stay 8-byte aligned");
   const uint32_t tid = threadIdx.x;
   const uint64_t rid_mask = a.key_shift >= 64 ? ~0ull : ((1ull << a.key_shift) - 1);
   const uint32_t hash_shift32 = a.shift_bits - 32;  // KS32: hash bits start inside the high word
@@ -1170,7 +1182,7 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
     if (v_nxt) issue(n_lo, n_hi, slot ^ 1, xs_nxt);
 
     const uint32_t r_n = (uint32_t)c_hi.x, s_n = (uint32_t)(c_hi.x >> 32), partition = (uint32_t)c_hi.y;
-    const uint32_t nb = r_n <= 1 ? 1u : (1u << (32 - __clz(r_n - 1)));
+    const uint32_t nb = r_n <= 1 ? 1u : min(1u << (32 - __clz(r_n - 1)), bucket_slots<CAP>());
     const uint32_t hmask = nb - 1;
     for (uint32_t i = tid; i < nb; i += TPB) bucket[i] = 0;
     __syncthreads();

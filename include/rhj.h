@@ -47,7 +47,7 @@ typedef struct rhj_config {
   uint32_t enable_two_level;    /* ENABLE_TWO_LEVEL_PARTITIONING (:28) */
   uint32_t tuple_bytes;         /* 16 = data/Tuple.h:15-22 {u64 key; u64 rid};
                                    8 = packed input, key in bits [32,64), rid in bits [0,32) */
-  uint32_t build_capacity;      /* tuples of one build slice held in shared memory: 0 = default (4096) */
+  uint32_t build_capacity;      /* tuples of one build slice held in shared memory (1024, 2048, 4096, 5120, 8192): 0 = default (5120) */
   double allocation_factor;     /* ALLOCATION_FACTOR (:35): receive-window head-room, >= 1.0 */
   uint32_t chunk_tuples;        /* tuples per scheduled chunk of the scatter passes, 0 = default */
   uint32_t flags;               /* RHJ_FLAG_* */
