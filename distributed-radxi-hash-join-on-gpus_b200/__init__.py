@@ -42,6 +42,7 @@ class Config(C.Structure):
 
 FLAG_HIST_WARP_AGGREGATE = 1
 FLAG_STAGE_HOST_INPUTS = 2
+FLAG_BALANCED_ASSIGNMENT = 4
 
 
 def make_config(network_fanout_bits=5, local_fanout_bits=5, payload_bits=27, enable_two_level=False,
@@ -120,6 +121,8 @@ SYMBOLS = {
     "rhj_memcpy_h2d": (_int, [_vp, _vp, _u64]),
     "rhj_host_assignment": (None, [_u32, _u32, _vp]),
     "rhj_host_offsets": (None, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "rhj_host_assignment_balanced": (None, [_vp, _vp, _u32, _u32, _vp]),
+    "rhj_host_offsets_assigned": (None, [_vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
 }
 
 

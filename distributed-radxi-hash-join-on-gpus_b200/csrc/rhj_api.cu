@@ -95,6 +95,7 @@ struct rhj_ctx {
   uint32_t *d_sub_cnt = nullptr;
   uint64_t *d_item_lstart = nullptr, *d_item_jcount = nullptr, *d_item_jstart = nullptr;
   unsigned long long *d_work = nullptr, *d_result = nullptr;
+  uint32_t *d_owned_list = nullptr, *d_slot_of = nullptr;  // partition <-> (owner, slot), see PlanNetworkArgs
   int *d_status = nullptr;
   ItemDesc *d_items = nullptr;
   uint64_t items_cap = 0;
@@ -150,6 +151,12 @@ static int validate_config(const rhj_config *c, int rank, int nranks) {
   uint32_t chunk = c->chunk_tuples ? c->chunk_tuples : kDefaultChunk;
   if (chunk % kTile != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kTile);
   return RHJ_OK;
+}
+
+// position of a rank's first partition in the owner-major partition list (k_plan_network)
+static uint32_t first_owned_slot(uint32_t P, int rank, int nranks) {
+  const uint32_t q = P / nranks, m = P % nranks;
+  return (uint32_t)rank * q + ((uint32_t)rank < m ? (uint32_t)rank : m);
 }
 
 static uint32_t owned_partitions(uint32_t P, int rank, int nranks) {
@@ -312,6 +319,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   }
   for (int i = 0; i < 6; ++i) add(2ull * P * 8);   // local, global, base, rel, abs, dest
   add((uint64_t)P * 4);                            // assignment
+  add((uint64_t)P * 4); add((uint64_t)P * 4);      // owned_list, slot_of
   add(2ull * nranks * 8);                          // window sizes
   add(2ull * nowned * 8); add(2ull * nowned * 8);  // part_off, part_cnt
   add(2ull * (nowned + 1) * 4);                    // cstart
@@ -393,6 +401,8 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_abs);
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_dest);
   if (!rc) rc = carve(ctx, (uint64_t)P, &ctx->d_assign);
+  if (!rc) rc = carve(ctx, (uint64_t)P, &ctx->d_owned_list);
+  if (!rc) rc = carve(ctx, (uint64_t)P, &ctx->d_slot_of);
   if (!rc) rc = carve(ctx, 2ull * ctx->nranks, &ctx->d_winsizes);
   if (!rc) rc = carve(ctx, 2ull * nowned, &ctx->d_part_off);
   if (!rc) rc = carve(ctx, 2ull * nowned, &ctx->d_part_cnt);
@@ -620,6 +630,9 @@ extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, v
   a.abs = ctx->d_abs;
   a.dest = ctx->d_dest;
   a.assignment = ctx->d_assign;
+  a.balanced = (ctx->cfg.flags & RHJ_FLAG_BALANCED_ASSIGNMENT) ? 1u : 0u;
+  a.owned_list = ctx->d_owned_list;
+  a.slot_of = ctx->d_slot_of;
   a.window_sizes = ctx->d_winsizes;
   a.nowned = ctx->nowned;
   a.part_off = ctx->d_part_off;
@@ -863,8 +876,7 @@ static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, b
     a.nowned = ctx->nowned;
     a.L = ctx->L;
     a.NS = ctx->NS;
-    a.rank = ctx->rank;
-    a.nranks = ctx->nranks;
+    a.owned = ctx->d_owned_list + first_owned_slot(ctx->P, ctx->rank, ctx->nranks);
     a.net_bits = ctx->cfg.network_fanout_bits;
     a.key_shift = ctx->key_shift;
     a.shift_bits = ctx->shift_bits;
@@ -927,16 +939,28 @@ extern "C" int rhj_get_write_offsets(rhj_ctx *ctx, int which, uint64_t *out_host
   return get_u64(ctx, which, ctx ? ctx->d_abs : nullptr, 2, out_host, stream);
 }
 
+// slot j of partition p among this rank's partitions, or an error if another rank owns it
+static int owned_slot(rhj_ctx *ctx, uint32_t p, uint32_t *j) {
+  if (p >= ctx->P) return fail(RHJ_ERR_INVALID, "partition %u outside [0,%u)", p, ctx->P);
+  uint32_t owner = 0;
+  int rc = copy_out(ctx, &owner, ctx->d_assign + p, 4, nullptr);
+  if (!rc) rc = copy_out(ctx, j, ctx->d_slot_of + p, 4, nullptr);
+  if (rc) return rc;
+  if (owner != (uint32_t)ctx->rank) return fail(RHJ_ERR_INVALID, "partition %u not owned by rank %d", p, ctx->rank);
+  return RHJ_OK;
+}
+
 extern "C" int rhj_get_local_partition(rhj_ctx *ctx, int which, uint32_t p, uint64_t *hist_host, uint64_t *prefix_host,
                                        void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 or 1");
   if (!ctx->cfg.enable_two_level) return fail(RHJ_ERR_STATE, "two-level partitioning is off");
   if (ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
-  if (p >= ctx->P || p % ctx->nranks != (uint32_t)ctx->rank) return fail(RHJ_ERR_INVALID, "partition %u not owned by rank %d", p, ctx->rank);
-  uint32_t j = p / ctx->nranks;
+  uint32_t j = 0;
+  int rc = owned_slot(ctx, p, &j);
+  if (rc) return rc;
   std::vector<uint32_t> cnt(ctx->L);
-  int rc = copy_out(ctx, cnt.data(), ctx->d_sub_cnt + (uint64_t)which * ctx->NS + (uint64_t)j * ctx->L, (size_t)ctx->L * 4, stream);
+  rc = copy_out(ctx, cnt.data(), ctx->d_sub_cnt + (uint64_t)which * ctx->NS + (uint64_t)j * ctx->L, (size_t)ctx->L * 4, stream);
   if (rc) return rc;
   if (hist_host)
     for (uint32_t l = 0; l < ctx->L; ++l) hist_host[l] = cnt[l];
@@ -951,10 +975,11 @@ extern "C" int rhj_get_partition_dev(rhj_ctx *ctx, int which, uint32_t p, int af
   if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 or 1");
   if (ctx->stage < (after_local_pass ? 4 : 3)) return fail(RHJ_ERR_STATE, "stage not reached");
   if (after_local_pass && !ctx->cfg.enable_two_level) return fail(RHJ_ERR_STATE, "two-level partitioning is off");
-  if (p >= ctx->P || p % ctx->nranks != (uint32_t)ctx->rank) return fail(RHJ_ERR_INVALID, "partition %u not owned by rank %d", p, ctx->rank);
-  uint32_t j = p / ctx->nranks;
+  uint32_t j = 0;
+  int rc = owned_slot(ctx, p, &j);
+  if (rc) return rc;
   uint64_t off = 0, cnt = 0;
-  int rc = copy_out(ctx, &off, ctx->d_part_off + (uint64_t)which * ctx->nowned + j, 8, nullptr);
+  rc = copy_out(ctx, &off, ctx->d_part_off + (uint64_t)which * ctx->nowned + j, 8, nullptr);
   if (!rc) rc = copy_out(ctx, &cnt, ctx->d_part_cnt + (uint64_t)which * ctx->nowned + j, 8, nullptr);
   if (rc) return rc;
   if (after_local_pass) {
@@ -1110,8 +1135,30 @@ extern "C" void rhj_host_assignment(uint32_t nranks, uint32_t parts, uint32_t *a
   for (uint32_t p = 0; p < parts; ++p) assignment[p] = p % nranks;  // histograms/AssignmentMap.cpp:41-43
 }
 
-extern "C" void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32_t rank, uint32_t parts, uint64_t *global,
-                                 uint64_t *base, uint64_t *rel, uint64_t *abs, uint64_t *window_sizes) {
+// The device version is in k_plan_network; both follow the same rule, stated in include/rhj.h.
+extern "C" void rhj_host_assignment_balanced(const uint64_t *global_inner, const uint64_t *global_outer, uint32_t nranks,
+                                             uint32_t parts, uint32_t *assignment) {
+  std::vector<std::pair<uint64_t, uint32_t>> order(parts);
+  for (uint32_t p = 0; p < parts; ++p) order[p] = {global_inner[p] + global_outer[p], p};
+  std::sort(order.begin(), order.end(), [](const std::pair<uint64_t, uint32_t> &a, const std::pair<uint64_t, uint32_t> &b) {
+    return a.first != b.first ? a.first > b.first : a.second < b.second;
+  });
+  std::vector<uint64_t> load(nranks, 0);
+  std::vector<uint32_t> room(nranks);
+  for (uint32_t r = 0; r < nranks; ++r) room[r] = parts / nranks + (r < parts % nranks ? 1u : 0u);
+  for (uint32_t i = 0; i < parts; ++i) {
+    uint32_t best = nranks;
+    for (uint32_t r = 0; r < nranks; ++r)
+      if (room[r] && (best == nranks || load[r] < load[best])) best = r;
+    assignment[order[i].second] = best;
+    load[best] += order[i].first;
+    room[best] -= 1;
+  }
+}
+
+extern "C" void rhj_host_offsets_assigned(const uint64_t *locals, const uint32_t *assignment, uint32_t nranks, uint32_t rank,
+                                          uint32_t parts, uint64_t *global, uint64_t *base, uint64_t *rel, uint64_t *abs,
+                                          uint64_t *window_sizes) {
   std::vector<uint64_t> running(nranks, 0);
   for (uint32_t p = 0; p < parts; ++p) {
     uint64_t g = 0, before = 0;
@@ -1120,7 +1167,7 @@ extern "C" void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32
       if (r < rank) before += v;  // histograms/OffsetMap.cpp:78-83 (exclusive scan over ranks)
       g += v;                     // histograms/GlobalHistogram.cpp:37-42
     }
-    uint32_t owner = p % nranks;
+    uint32_t owner = assignment[p];
     if (global) global[p] = g;
     if (base) base[p] = running[owner];  // histograms/OffsetMap.cpp:59-73
     if (rel) rel[p] = before;
@@ -1129,6 +1176,13 @@ extern "C" void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32
   }
   if (window_sizes)
     for (uint32_t r = 0; r < nranks; ++r) window_sizes[r] = running[r];  // data/Window.cpp:168-178
+}
+
+extern "C" void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32_t rank, uint32_t parts, uint64_t *global,
+                                 uint64_t *base, uint64_t *rel, uint64_t *abs, uint64_t *window_sizes) {
+  std::vector<uint32_t> assignment(parts);
+  rhj_host_assignment(nranks, parts, assignment.data());
+  rhj_host_offsets_assigned(locals, assignment.data(), nranks, rank, parts, global, base, rel, abs, window_sizes);
 }
 
 // -----------------------------------------------------------------------------------

@@ -500,7 +500,14 @@ struct PlanNetworkArgs {
   uint64_t *global_hist, *base, *rel, *abs, *dest;
   uint32_t *assignment;    // [P]
   uint64_t *window_sizes;  // [2][nranks]
-  // owned partitions (index j <-> partition rank + j*nranks)
+  // Partition -> owner.  0: p % n (AssignmentMap.cpp:41-43).  1: size-balanced (no counterpart in
+  // the reference's built code): partitions by descending global inner+outer count go to the
+  // least-loaded rank that still has a free slot; every rank keeps exactly the number of
+  // partitions p % n would give it, so all workspace sizes stay static.
+  uint32_t balanced;
+  uint32_t *owned_list;  // [P] partitions in owner-major order, ascending inside one owner
+  uint32_t *slot_of;     // [P] index of the partition among its owner's partitions
+  // owned partitions (index j <-> partition owned_list[first slot of this rank + j])
   uint32_t nowned;
   uint64_t *part_off;   // [2][nowned]
   uint64_t *part_cnt;   // [2][nowned]
@@ -520,8 +527,9 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
   __shared__ uint32_t tmp32[33];
   const uint32_t P = a.parts, n = a.nranks, me = a.rank, tid = threadIdx.x;
   const uint32_t q = P / n, m = P % n;  // owner r holds q + (r < m) partitions
-  for (int k = 0; k < 2; ++k) {
-    // GlobalHistogram.cpp:37-42 (sum over ranks) and OffsetMap.cpp:78-83 (exclusive scan over ranks)
+  auto first_slot = [&](uint32_t r) { return r * q + (r < m ? r : m); };
+  // GlobalHistogram.cpp:37-42 (sum over ranks) and OffsetMap.cpp:78-83 (exclusive scan over ranks)
+  for (int k = 0; k < 2; ++k)
     for (uint32_t p = tid; p < P; p += blockDim.x) {
       uint64_t g = 0, before = 0;
       for (uint32_t r = 0; r < n; ++r) {
@@ -531,20 +539,82 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
       }
       a.global_hist[k * P + p] = g;
       a.rel[k * P + p] = before;
-      if (k == 0) a.assignment[p] = p % n;  // AssignmentMap.cpp:41-43
+    }
+  __syncthreads();
+  if (!a.balanced || n == 1) {
+    for (uint32_t p = tid; p < P; p += blockDim.x) {
+      a.assignment[p] = p % n;  // AssignmentMap.cpp:41-43
+      a.slot_of[p] = p / n;
+      a.owned_list[first_slot(p % n) + p / n] = p;
+    }
+  } else {
+    // sort (weight descending, partition ascending): ascending bitonic sort of (~weight, p) keys
+    constexpr uint64_t kWMax = 0xFFFFFFFFFFFFull;
+    for (uint32_t p = tid; p < P; p += blockDim.x) {
+      const uint64_t w = a.global_hist[p] + a.global_hist[P + p];
+      sh_scan[p] = ((kWMax - (w < kWMax ? w : kWMax)) << 16) | p;
     }
     __syncthreads();
+    for (uint32_t size = 2; size <= P; size <<= 1)
+      for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+        for (uint32_t t = tid; t < P / 2; t += blockDim.x) {
+          const uint32_t lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+          const bool up = (lo & size) == 0;
+          const uint64_t x = sh_scan[lo], y = sh_scan[hi];
+          if ((x > y) == up) {
+            sh_scan[lo] = y;
+            sh_scan[hi] = x;
+          }
+        }
+        __syncthreads();
+      }
+    if (tid < 32) {  // greedy placement; lane l keeps the load and free slots of ranks l and l + 32
+      const uint32_t lane = tid;
+      uint64_t load0 = 0, load1 = 0;
+      uint32_t room0 = lane < n ? q + (lane < m ? 1u : 0u) : 0u;
+      uint32_t room1 = lane + 32 < n ? q + (lane + 32 < m ? 1u : 0u) : 0u;
+      for (uint32_t i = 0; i < P; ++i) {
+        const uint64_t key = sh_scan[i];
+        const uint32_t p = (uint32_t)(key & 0xFFFF);
+        const uint64_t w = kWMax - (key >> 16);
+        uint64_t c = ~0ull;
+        if (room0) c = (load0 << 6) | lane;
+        if (room1 && ((load1 << 6) | (lane + 32)) < c) c = (load1 << 6) | (lane + 32);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          const uint64_t o = __shfl_xor_sync(0xFFFFFFFFu, c, off);
+          c = o < c ? o : c;
+        }
+        const uint32_t best = (uint32_t)(c & 63);
+        if (best == lane) {
+          load0 += w;
+          room0 -= 1;
+        } else if (best == lane + 32) {
+          load1 += w;
+          room1 -= 1;
+        }
+        if (lane == 0) a.assignment[p] = best;
+      }
+    }
+    __syncthreads();
+    if (tid < n) {  // slots in ascending partition order
+      uint32_t c = 0;
+      const uint32_t s0 = first_slot(tid);
+      for (uint32_t p = 0; p < P; ++p)
+        if (a.assignment[p] == tid) {
+          a.slot_of[p] = c;
+          a.owned_list[s0 + c] = p;
+          ++c;
+        }
+    }
+  }
+  __syncthreads();
+  for (int k = 0; k < 2; ++k) {
     // OffsetMap.cpp:59-73: running sum per owner == exclusive scan in owner-major order
     uint64_t carry = 0;
     for (uint32_t i0 = 0; i0 < P; i0 += blockDim.x) {
       uint32_t i = i0 + tid;
-      uint64_t v = 0;
-      if (i < P) {
-        uint32_t r, j;
-        if (i < m * (q + 1)) { r = i / (q + 1); j = i % (q + 1); }
-        else { r = m + (i - m * (q + 1)) / q; j = (i - m * (q + 1)) % q; }
-        v = a.global_hist[k * P + r + j * n];
-      }
+      uint64_t v = i < P ? a.global_hist[k * P + a.owned_list[i]] : 0;
       uint64_t total;
       uint64_t ex = block_exclusive_scan<uint64_t>(v, tmp64, &total);
       if (i < P) sh_scan[i] = carry + ex;
@@ -553,33 +623,29 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
     if (tid == 0) sh_scan[P] = carry;
     __syncthreads();
     for (uint32_t p = tid; p < P; p += blockDim.x) {
-      uint32_t r = p % n, j = p / n;
-      uint32_t ostart = r * q + (r < m ? r : m);
-      uint64_t bs = sh_scan[ostart + j] - sh_scan[ostart];
+      const uint32_t r = a.assignment[p], ostart = first_slot(r);
+      uint64_t bs = sh_scan[ostart + a.slot_of[p]] - sh_scan[ostart];
       uint64_t ab = bs + a.rel[k * P + p];
       a.base[k * P + p] = bs;
       a.abs[k * P + p] = ab;  // OffsetMap.cpp:87-93
       a.dest[k * P + p] = a.peer_window[k][r] + ab * 8;
     }
     for (uint32_t r = tid; r < n; r += blockDim.x) {
-      uint32_t ostart = r * q + (r < m ? r : m);
-      uint32_t oend = (r + 1) * q + (r + 1 < m ? r + 1 : m);
-      uint64_t ws = sh_scan[oend] - sh_scan[ostart];  // data/Window.cpp:168-178
+      uint64_t ws = sh_scan[first_slot(r + 1)] - sh_scan[first_slot(r)];  // data/Window.cpp:168-178
       a.window_sizes[k * n + r] = ws;
       if (ws > a.window_cap[k]) atomicMax(a.status, (int)kDevWindowOverflow);
     }
     __syncthreads();
     // owned partitions and their local-pass chunking
     uint32_t ccarry = 0;
+    const uint32_t mine = first_slot(me);
     for (uint32_t j0 = 0; j0 < a.nowned; j0 += blockDim.x) {
       uint32_t j = j0 + tid;
       uint32_t nch = 0;
       if (j < a.nowned) {
-        uint32_t p = me + j * n;
+        const uint32_t p = a.owned_list[mine + j];
         uint64_t cnt = a.global_hist[k * P + p];
-        uint32_t r = p % n, jj = p / n;
-        uint32_t ostart = r * q + (r < m ? r : m);
-        a.part_off[k * a.nowned + j] = sh_scan[ostart + jj] - sh_scan[ostart];
+        a.part_off[k * a.nowned + j] = sh_scan[mine + j] - sh_scan[mine];
         a.part_cnt[k * a.nowned + j] = cnt;
         nch = (uint32_t)((cnt + a.chunk2 - 1) / a.chunk2);
       }
@@ -598,7 +664,7 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
       uint64_t scarry = 0;
       for (uint32_t i0 = 0; i0 < P; i0 += blockDim.x) {
         const uint32_t i = i0 + tid;
-        const uint64_t v = (i < P && i % n != me) ? a.gathered[((uint64_t)me * 2 + k) * P + i] : 0;
+        const uint64_t v = (i < P && a.assignment[i] != me) ? a.gathered[((uint64_t)me * 2 + k) * P + i] : 0;
         uint64_t total;
         const uint64_t ex = block_exclusive_scan<uint64_t>(v, tmp64, &total);
         if (i < P) sh_scan[i] = scarry + ex;
@@ -606,7 +672,7 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
       }
       __syncthreads();
       for (uint32_t p = tid; p < P; p += blockDim.x) {
-        const bool remote = p % n != me;
+        const bool remote = a.assignment[p] != me;
         const uint64_t src = a.stage_base[k] + sh_scan[p] * 8;
         a.push_cnt[k * P + p] = remote ? a.gathered[((uint64_t)me * 2 + k) * P + p] : 0;
         a.push_src[k * P + p] = src;
@@ -879,7 +945,7 @@ struct BuildProbeArgs {
   unsigned long long *work_counter;
   unsigned long long *result;   // [5]
   uint32_t nowned, L, NS;
-  uint32_t rank, nranks;
+  const uint32_t *owned;  // [nowned] network partition id of the j-th owned partition
   uint32_t net_bits, key_shift, shift_bits;
   uint32_t sslice;
   const int *status;
@@ -917,7 +983,7 @@ __device__ __forceinline__ ItemDesc resolve_item(const BuildProbeArgs &a, uint64
   d.s_off = a.sub_off[a.NS + sp] + (uint64_t)si * a.sslice;
   d.r_n = min((uint32_t)CAP, cnt_r - ri * CAP);
   d.s_n = min(a.sslice, cnt_s - si * a.sslice);
-  d.partition = a.rank + j * a.nranks;
+  d.partition = a.owned[j];
   d.pad = 0;
   return d;
 }
@@ -940,7 +1006,7 @@ __global__ void __launch_bounds__(256) k_expand_items(BuildProbeArgs a, ItemDesc
       d.s_off = a.sub_off[a.NS + sp] + (uint64_t)si * a.sslice;
       d.r_n = min((uint32_t)CAP, cnt_r - ri * CAP);
       d.s_n = min(a.sslice, cnt_s - si * a.sslice);
-      d.partition = a.rank + j * a.nranks;
+      d.partition = a.owned[j];
       d.pad = 0;
       out[idx] = d;
     }
@@ -1003,7 +1069,7 @@ __global__ void __launch_bounds__(kBpTPB) k_build_probe(BuildProbeArgs a) {
     const uint32_t s_begin = si * a.sslice, s_n = min(a.sslice, cnt_s - s_begin);
     const uint64_t *rp = a.src[0] + a.sub_off[sp] + r_begin;
     const uint64_t *sp_ptr = a.src[1] + a.sub_off[a.NS + sp] + s_begin;
-    const uint32_t partition = a.rank + j * a.nranks;
+    const uint32_t partition = a.owned[j];
 
     // table size: next power of two of the slice (BuildProbe.cpp:59-60 uses the partition size)
     uint32_t nb = 1;

@@ -55,6 +55,14 @@ typedef struct rhj_config {
 
 #define RHJ_FLAG_HIST_WARP_AGGREGATE 1u /* warp-aggregate the histogram atomics (skew-proof) */
 #define RHJ_FLAG_STAGE_HOST_INPUTS 2u    /* rhj_plan also reserves device staging for rhj_join_host */
+/* Size-balanced partition -> rank assignment instead of AssignmentMap.cpp:41-43's p % n (which
+ * receives the histograms but ignores them).  Rule, identical on every rank:
+ * partitions in order of descending global inner+outer tuple count (ties: ascending id) each go to
+ * the rank with the least tuples so far (ties: lowest rank) among the ranks that still have a free
+ * slot; rank r has P/n + (r < P%n) slots, exactly as many partitions as p % n gives it.  Offsets
+ * keep the reference's definition (OffsetMap.cpp:59-93) under the new owners.  All ranks of a join
+ * must set the flag alike. */
+#define RHJ_FLAG_BALANCED_ASSIGNMENT 4u
 
 /* Join result: the reference only counts (HashJoin::RESULT_COUNTER, operators/HashJoin.cpp:28,
  * tasks/BuildProbe.cpp:97-115).  The sums are an order-independent checksum over
@@ -261,6 +269,13 @@ int rhj_memcpy_h2d(void *dst_dev, const void *src_host, uint64_t bytes);
 void rhj_host_assignment(uint32_t nranks, uint32_t parts, uint32_t *assignment);
 void rhj_host_offsets(const uint64_t *locals, uint32_t nranks, uint32_t rank, uint32_t parts, uint64_t *global,
                       uint64_t *base, uint64_t *rel, uint64_t *abs, uint64_t *window_sizes);
+/* The same under RHJ_FLAG_BALANCED_ASSIGNMENT: the assignment from the two global histograms
+ * (u64[P] each), and the offsets of one relation for a given assignment. */
+void rhj_host_assignment_balanced(const uint64_t *global_inner, const uint64_t *global_outer, uint32_t nranks,
+                                  uint32_t parts, uint32_t *assignment);
+void rhj_host_offsets_assigned(const uint64_t *locals, const uint32_t *assignment, uint32_t nranks, uint32_t rank,
+                               uint32_t parts, uint64_t *global, uint64_t *base, uint64_t *rel, uint64_t *abs,
+                               uint64_t *window_sizes);
 
 #ifdef __cplusplus
 }

@@ -192,6 +192,41 @@ void orc_assignment(uint32_t nranks, uint32_t parts, uint32_t *assignment) {
   for (uint32_t p = 0; p < parts; ++p) assignment[p] = p % nranks;
 }
 
+typedef struct {
+  uint64_t w;
+  uint32_t p;
+} weighted_part;
+
+static int cmp_weight_desc(const void *a, const void *b) {
+  const weighted_part *x = (const weighted_part *)a, *y = (const weighted_part *)b;
+  if (x->w != y->w) return x->w > y->w ? -1 : 1;
+  return x->p < y->p ? -1 : (x->p > y->p);
+}
+
+void orc_assignment_balanced(const uint64_t *global_inner, const uint64_t *global_outer, uint32_t nranks,
+                             uint32_t parts, uint32_t *assignment) {
+  weighted_part *wp = (weighted_part *)malloc(parts * sizeof(weighted_part));
+  uint64_t *load = (uint64_t *)calloc(nranks, sizeof(uint64_t));
+  uint32_t *room = (uint32_t *)malloc(nranks * sizeof(uint32_t));
+  for (uint32_t p = 0; p < parts; ++p) {
+    wp[p].w = global_inner[p] + global_outer[p];
+    wp[p].p = p;
+  }
+  qsort(wp, parts, sizeof(weighted_part), cmp_weight_desc);
+  for (uint32_t r = 0; r < nranks; ++r) room[r] = parts / nranks + (r < parts % nranks ? 1u : 0u);
+  for (uint32_t i = 0; i < parts; ++i) {
+    uint32_t best = nranks;
+    for (uint32_t r = 0; r < nranks; ++r)
+      if (room[r] > 0 && (best == nranks || load[r] < load[best])) best = r;
+    assignment[wp[i].p] = best;
+    load[best] += wp[i].w;
+    room[best] -= 1;
+  }
+  free(wp);
+  free(load);
+  free(room);
+}
+
 /* histograms/OffsetMap.cpp:59-73 (base: running sum per owner),
  * :75-85 (relative: MPI_Exscan over ranks; rank 0 keeps calloc's zero),
  * :87-93 (absolute = base + relative).  Units: tuples. */
@@ -415,13 +450,16 @@ int orc_join_pairs(const orc_tuple *const *inner, const uint64_t *inner_n, const
   const orc_tuple *const *rel[2] = {inner, outer};
   const uint64_t *rel_n[2] = {inner_n, outer_n};
 
-  orc_assignment(nranks, parts, assign);
   for (int k = 0; k < 2; ++k) {
     loc[k] = (uint64_t *)malloc((uint64_t)nranks * parts * sizeof(uint64_t));
     glob[k] = (uint64_t *)malloc(parts * sizeof(uint64_t));
     for (uint32_t r = 0; r < nranks; ++r)
       orc_local_histogram(rel[k][r], rel_n[k][r], cfg, loc[k] + (uint64_t)r * parts);
     orc_global_histogram(loc[k], nranks, parts, glob[k]);
+  }
+  if (cfg->balanced) orc_assignment_balanced(glob[0], glob[1], nranks, parts, assign);
+  else orc_assignment(nranks, parts, assign);
+  for (int k = 0; k < 2; ++k) {
     win[k] = (uint64_t **)malloc(nranks * sizeof(uint64_t *));
     for (uint32_t r = 0; r < nranks; ++r) {
       uint64_t ws = orc_window_size(glob[k], assign, parts, r);

@@ -35,6 +35,8 @@ typedef struct {
   uint32_t loc_bits;     /* LOCAL_PARTITIONING_FANOUT */
   uint32_t payload_bits; /* PAYLOAD_BITS */
   uint32_t two_level;    /* ENABLE_TWO_LEVEL_PARTITIONING */
+  uint32_t balanced;     /* 0: AssignmentMap.cpp's p % n; 1: size-balanced assignment (SURVEY.md 8(f3),
+                            no counterpart in the reference's built code) */
 } orc_config;
 
 /* Result of a join: the reference only counts (tasks/BuildProbe.cpp:97-115);
@@ -77,6 +79,11 @@ void orc_fill_zipf(orc_tuple *t, uint64_t n, uint64_t first, uint64_t domain, do
 void orc_local_histogram(const orc_tuple *t, uint64_t n, const orc_config *cfg, uint64_t *hist);
 void orc_global_histogram(const uint64_t *locals, uint32_t nranks, uint32_t parts, uint64_t *global);
 void orc_assignment(uint32_t nranks, uint32_t parts, uint32_t *assignment);
+/* Size-balanced assignment: partitions by descending weight (global inner + outer count, ties by
+ * ascending id) go to the least-loaded rank (ties: lowest rank) that still has a free slot, every
+ * rank keeping exactly the number of partitions the round-robin map gives it. */
+void orc_assignment_balanced(const uint64_t *global_inner, const uint64_t *global_outer, uint32_t nranks,
+                             uint32_t parts, uint32_t *assignment);
 void orc_offsets(const uint64_t *locals, const uint64_t *global, const uint32_t *assignment,
                  uint32_t nranks, uint32_t rank, uint32_t parts, uint64_t *base, uint64_t *rel,
                  uint64_t *abs);

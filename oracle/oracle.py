@@ -28,7 +28,7 @@ class Config(C.Structure):
     """core/Configuration.h:28-37 knobs that change results."""
 
     _fields_ = [("net_bits", C.c_uint32), ("loc_bits", C.c_uint32),
-                ("payload_bits", C.c_uint32), ("two_level", C.c_uint32)]
+                ("payload_bits", C.c_uint32), ("two_level", C.c_uint32), ("balanced", C.c_uint32)]
 
     def tag(self) -> str:
         return f"n{self.net_bits}_l{self.loc_bits}_p{self.payload_bits}_t{self.two_level}"
@@ -79,6 +79,7 @@ def lib():
         L.orc_local_histogram.argtypes = [vp, u64, cfgp, vp]
         L.orc_global_histogram.argtypes = [vp, u32, u32, vp]
         L.orc_assignment.argtypes = [u32, u32, vp]
+        L.orc_assignment_balanced.argtypes = [vp, vp, u32, u32, vp]
         L.orc_offsets.argtypes = [vp, vp, vp, u32, u32, u32, vp, vp, vp]
         L.orc_window_size.restype = u64
         L.orc_window_size.argtypes = [vp, vp, u32, u32]
@@ -187,14 +188,26 @@ class Plan:
     window_size: np.ndarray  # [nranks]
 
 
-def plan(locals_: np.ndarray, nranks: int) -> Plan:
+def balanced_assignment(global_inner: np.ndarray, global_outer: np.ndarray, nranks: int) -> np.ndarray:
+    gi = np.ascontiguousarray(global_inner, np.uint64)
+    go = np.ascontiguousarray(global_outer, np.uint64)
+    assign = np.zeros(len(gi), np.uint32)
+    lib().orc_assignment_balanced(_p(gi), _p(go), nranks, len(gi), _p(assign))
+    return assign
+
+
+def plan(locals_: np.ndarray, nranks: int, assignment: np.ndarray | None = None) -> Plan:
+    """Histogram phase of one relation; `assignment` (e.g. from balanced_assignment) overrides p % n."""
     L = lib()
     locals_ = np.ascontiguousarray(locals_, np.uint64).reshape(nranks, -1)
     parts = locals_.shape[1]
     glob = np.zeros(parts, np.uint64)
     L.orc_global_histogram(_p(locals_), nranks, parts, _p(glob))
     assign = np.zeros(parts, np.uint32)
-    L.orc_assignment(nranks, parts, _p(assign))
+    if assignment is None:
+        L.orc_assignment(nranks, parts, _p(assign))
+    else:
+        assign[:] = assignment
     base = np.zeros(parts, np.uint64)
     rel = np.zeros((nranks, parts), np.uint64)
     ab = np.zeros((nranks, parts), np.uint64)

@@ -6,7 +6,8 @@ import numpy as np
 
 
 def ocfg(O, cfg):
-    return O.Config(cfg.network_fanout_bits, cfg.local_fanout_bits, cfg.payload_bits, cfg.enable_two_level)
+    return O.Config(cfg.network_fanout_bits, cfg.local_fanout_bits, cfg.payload_bits, cfg.enable_two_level,
+                    1 if cfg.flags & 4 else 0)  # RHJ_FLAG_BALANCED_ASSIGNMENT
 
 
 def to_input(arr, tuple_bytes):
@@ -89,9 +90,13 @@ def check_against_oracle(rhj, O, cfg, inner, outer, deep=True):
         run.histogram()
         run.offsets()
         plans = []
+        assignment = None
+        if oc.balanced:
+            glob = [np.sum([O.local_histogram(t, oc) for t in rels], axis=0, dtype=np.uint64) for rels in (inner, outer)]
+            assignment = O.balanced_assignment(glob[0], glob[1], n)
         for which, rels in ((0, inner), (1, outer)):
             loc = np.stack([O.local_histogram(t, oc) for t in rels])
-            pl = O.plan(loc, n)
+            pl = O.plan(loc, n, assignment)
             plans.append(pl)
             for r, c in enumerate(run.ctx):
                 assert np.array_equal(c.get_local_histogram(which), loc[r]), f"local histogram rel {which} rank {r}"

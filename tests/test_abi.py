@@ -92,3 +92,33 @@ def test_host_offsets_equal_oracle(rhj, oracle, nranks, parts):
         assert np.array_equal(g, pl.global_) and np.array_equal(b, pl.base)
         assert np.array_equal(rel, pl.rel[r]) and np.array_equal(ab, pl.abs_[r])
         assert np.array_equal(ws, pl.window_size)
+
+
+@pytest.mark.parametrize("nranks,parts", [(2, 32), (3, 32), (4, 256), (8, 512), (5, 8), (40, 64)])
+def test_host_balanced_assignment_equals_oracle(rhj, oracle, nranks, parts):
+    """RHJ_FLAG_BALANCED_ASSIGNMENT's rule on the host (rhj_host_assignment_balanced,
+    rhj_host_offsets_assigned) against the oracle's statement of it, on skewed histograms with ties."""
+    rng = np.random.default_rng(nranks * 7 + parts)
+    loc_i = rng.integers(0, 50, (nranks, parts)).astype(np.uint64)          # many ties
+    loc_o = (rng.zipf(1.3, (nranks, parts)) % 100000).astype(np.uint64)     # a few very heavy partitions
+    gi, go = loc_i.sum(0, dtype=np.uint64), loc_o.sum(0, dtype=np.uint64)
+    want = oracle.balanced_assignment(gi, go, nranks)
+    L = rhj.lib()
+    a = np.zeros(parts, np.uint32)
+    L.rhj_host_assignment_balanced(gi.ctypes.data, go.ctypes.data, nranks, parts, a.ctypes.data)
+    assert np.array_equal(a, want)
+    # every rank keeps the number of partitions p % n gives it
+    assert np.array_equal(np.bincount(a, minlength=nranks), np.bincount(np.arange(parts) % nranks, minlength=nranks))
+    # and the heaviest rank is no heavier than under p % n
+    w = (gi + go).astype(np.float64)
+    assert np.bincount(a, w, nranks).max() <= np.bincount(np.arange(parts) % nranks, w, nranks).max()
+    for loc in (loc_i, loc_o):
+        pl = oracle.plan(loc, nranks, want)
+        for r in range(nranks):
+            g, b, rel, ab = (np.zeros(parts, np.uint64) for _ in range(4))
+            ws = np.zeros(nranks, np.uint64)
+            L.rhj_host_offsets_assigned(loc.ctypes.data, a.ctypes.data, nranks, r, parts, g.ctypes.data, b.ctypes.data,
+                                        rel.ctypes.data, ab.ctypes.data, ws.ctypes.data)
+            assert np.array_equal(g, pl.global_) and np.array_equal(b, pl.base)
+            assert np.array_equal(rel, pl.rel[r]) and np.array_equal(ab, pl.abs_[r])
+            assert np.array_equal(ws, pl.window_size)

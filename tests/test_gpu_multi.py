@@ -101,11 +101,13 @@ def _worker_config(rank, world, port, shape, log2n, out_dir):
         rhj.fill_perm(ds, 8, ns, rank * ns, NS, seed=32, modulo=NR, start_rid=rank * ns)
         want = (NS, 16 * (NR * (NR - 1) // 2) & m64, 16 * (NR * (NR - 1) // 2) & m64, NS * (NS - 1) // 2 & m64)
         tb, caps = 8, (2 * nr, 2 * ns)
-    else:  # "c4": Zipf(1)-like probe keys (P(k) ~ 1/k), unique build keys covering the whole domain
+    else:  # "c4": Zipf(1)-like probe keys (P(k) ~ 1/k), unique build keys covering the whole domain;
+        # "c4_balanced": the same with RHJ_FLAG_BALANCED_ASSIGNMENT
         n = 1 << log2n
         nr = ns = n
         NR = NS = n * world
-        cfg = rhj.make_config(net, loc, 32 - net, True)
+        cfg = rhj.make_config(net, loc, 32 - net, True,
+                              flags=rhj.FLAG_BALANCED_ASSIGNMENT if shape == "c4_balanced" else 0)
         dr = torch.empty(2 * n, dtype=torch.int64, device=dev)
         ds = torch.empty(2 * n, dtype=torch.int64, device=dev)
         rhj.fill_perm(dr, 16, n, rank * n, NR, seed=41, start_rid=rank * n)
@@ -152,7 +154,7 @@ def _worker_config(rank, world, port, shape, log2n, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("shape", ["c5", "c4"])
+@pytest.mark.parametrize("shape", ["c5", "c4", "c4_balanced"])
 def test_baseline_configs_4_and_5_full_size_all_gpus(tmp_path, shape):
     """256 M probe tuples per GPU on every GPU of the box (2, 4 or 8)."""
     import json

@@ -165,3 +165,24 @@ def test_zipf_outer(rhj, oracle):
     inner = oracle.fill_perm(n, 0, n, seed=41)
     outer = oracle.fill_zipf(n, 0, n, 1.0, seed=42)
     check_against_oracle(rhj, oracle, rhj.make_config(6, 6, 26, True), [inner], [outer], deep=False)
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 4])
+@pytest.mark.parametrize("two_level", [True, False])
+def test_balanced_assignment_all_stages(rhj, oracle, nranks, two_level):
+    """RHJ_FLAG_BALANCED_ASSIGNMENT: assignment, offsets, windows, local partitions and per-rank results
+    equal the oracle's under the same rule (skewed probe side, so the assignment differs from p % n)."""
+    cfg = rhj.make_config(4, 3, 28, two_level, flags=rhj.FLAG_BALANCED_ASSIGNMENT)
+    inner = [oracle.fill_perm(6000, r * 6000, 6000 * nranks, seed=9) for r in range(nranks)]
+    outer = [oracle.fill_zipf(20000, r * 20000, 6000 * nranks, 1.0, seed=10 + r) for r in range(nranks)]
+    res = check_against_oracle(rhj, oracle, cfg, inner, outer)
+    plain = oracle.join(inner, outer, oracle.Config(4, 3, 28, two_level, 0))
+    assert oracle.total(res) == oracle.total(plain)
+    assert [r.matches for r in res] != [r.matches for r in plain]
+
+
+def test_balanced_assignment_ties_and_uniform_sizes(rhj, oracle):
+    """All partitions equally heavy (dense unique keys): every step of the greedy rule is a tie."""
+    cfg = rhj.make_config(5, 4, 27, True, flags=rhj.FLAG_BALANCED_ASSIGNMENT)
+    inner, outer = oracle.generate_reference(3, 30000, 30000)
+    check_against_oracle(rhj, oracle, cfg, inner, outer)

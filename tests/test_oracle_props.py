@@ -111,3 +111,18 @@ def test_materialised_pairs_equal_an_independent_equi_join(oracle, two_level):
     res2, pairs2 = oracle.join_pairs(inner, outer, cfg, 10)
     assert [r.astuple() for r in res2] == [r.astuple() for r in res]
     assert all(len(p) == min(10, r.matches) for p, r in zip(pairs2, res2))
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 4])
+def test_balanced_assignment_moves_partitions_not_results(oracle, nranks):
+    """Under the size-balanced assignment (orc_config.balanced) each rank joins other partitions, so
+    per-rank results change, but their sum is the join of the same relations: equal to p % n's sum and
+    to the sort-merge checker; on a skewed probe side the busiest rank gets less than under p % n."""
+    inner = [oracle.fill_perm(6000, r * 6000, 6000 * nranks, seed=9) for r in range(nranks)]
+    outer = [oracle.fill_zipf(20000, r * 20000, 6000 * nranks, 1.0, seed=10 + r) for r in range(nranks)]
+    rr = oracle.join(inner, outer, oracle.Config(4, 3, 28, True, 0))
+    bal = oracle.join(inner, outer, oracle.Config(4, 3, 28, True, 1))
+    assert oracle.total(rr) == oracle.total(bal)
+    assert oracle.total(bal) == oracle.bruteforce(np.concatenate(inner), np.concatenate(outer)).astuple()
+    assert max(r.matches for r in bal) <= max(r.matches for r in rr)
+    assert [r.matches for r in bal] != [r.matches for r in rr]
