@@ -196,6 +196,16 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   c->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
   if (const char *e = getenv("RHJ_SCATTER")) c->tune_scatter = strcmp(e, "legacy") == 0 ? 0 : 2;
+  // The offset-driven kernels hold two staged tiles plus three per-bin slot arrays in shared
+  // memory, which stops fitting above 2048 bins; wider fan-outs run on the first-generation pair
+  // (k_histogram + k_scatter: one staged tile, per-tile scan).
+  {
+    const size_t smem_limit = 227 * 1024;
+    const bool net_fits = (cfg->tuple_bytes == 16 ? scatter3_smem_bytes<InputSource<16>>(c->P)
+                                                  : scatter3_smem_bytes<InputSource<8>>(c->P)) <= smem_limit;
+    const bool loc_fits = !cfg->enable_two_level || scatter3_smem_bytes<ValueSource>(c->L) <= smem_limit;
+    if (!net_fits || !loc_fits) c->tune_scatter = 0;
+  }
   if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
   if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = std::max(0, std::min(32, atoi(e)));
   if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));

@@ -11,9 +11,11 @@
 //                          (data/Window.cpp:108-115, MPI_Put)
 //   Kq  k_plan_local/items LocalPartitioning.cpp:165-192 (8-tuple padded prefix) + work list
 //   K4  k_build_probe3     BuildProbe.cpp:47-121
-//   k_histogram, k_scatter, k_build_probe are the first-generation kernels, kept selectable
-//   (RHJ_SCATTER=legacy, RHJ_BP=legacy) as the ablation baseline; k_histogram also serves the
-//   allocation-free entry point.
+//   k_histogram, k_scatter, k_build_probe are the first-generation kernels.  They run fan-outs of
+//   more than 2048 bins per pass (the offset-driven pair's shared-memory arrays stop fitting),
+//   single-pass mode and work items beyond the expanded list (k_build_probe), the allocation-free
+//   histogram entry point (k_histogram), and stay selectable as the ablation baseline
+//   (RHJ_SCATTER=legacy, RHJ_BP=legacy).
 //
 // All stages are HBM-bound integer work (no tensor cores).  Work is cut into
 // fixed-size chunks of consecutive tuples; the histogram and the scatter of a pass

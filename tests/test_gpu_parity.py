@@ -186,3 +186,15 @@ def test_balanced_assignment_ties_and_uniform_sizes(rhj, oracle):
     cfg = rhj.make_config(5, 4, 27, True, flags=rhj.FLAG_BALANCED_ASSIGNMENT)
     inner, outer = oracle.generate_reference(3, 30000, 30000)
     check_against_oracle(rhj, oracle, cfg, inner, outer)
+
+
+@pytest.mark.parametrize("knobs", [(12, 3, 20, True), (3, 12, 20, True), (12, 12, 8, True), (12, 5, 20, False)])
+def test_fan_out_of_4096_partitions(rhj, oracle, knobs):
+    """The widest fan-out the configuration accepts (12 bits per pass) does not fit the offset-driven
+    scatter's shared memory; the library switches to its first-generation kernels by itself."""
+    cfg = rhj.make_config(*knobs)
+    inner, outer = oracle.generate_reference(2, 50000, 50000)
+    check_against_oracle(rhj, oracle, cfg, inner, outer, deep=False)
+    inner = [oracle.fill_perm(40000, 0, 40000, seed=4)]
+    outer = [oracle.fill_zipf(90000, 0, 40000, 1.0, seed=6)]
+    check_against_oracle(rhj, oracle, cfg, inner, outer, deep=(knobs != (12, 12, 8, True)))
