@@ -83,8 +83,10 @@ def _host_barrier_group(group=None):
     return _HOST_GROUPS[key]
 
 
-def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None):
-    """operators/HashJoin.cpp:45-220 for this rank; every rank calls it (collective)."""
+def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=None, capacity=None):
+    """operators/HashJoin.cpp:45-220 for this rank; every rank calls it (collective).  With `pairs`
+    (device int64 tensor, 2 values per pair) the build/probe stage also writes this rank's
+    (rid_R, rid_S) pairs (rhj_build_probe_pairs)."""
     import torch
     import torch.distributed as dist
     ctx.histogram(inner.data, inner.local_size, outer.data, outer.local_size)
@@ -114,7 +116,10 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None):
             ctx.local_partition_rel(which)
     else:
         ctx.local_partition()
-    ctx.build_probe()
+    if pairs is not None:
+        ctx.build_probe_pairs(pairs, capacity)
+    else:
+        ctx.build_probe()
 
 
 class HashJoin:
@@ -138,8 +143,9 @@ class HashJoin:
         self.ctx.plan(innerRelation.local_size, outerRelation.local_size, *window_caps)
         exchange_windows(self.ctx, group)
 
-    def join(self):
-        join_multi_rank(self.ctx, self.innerRelation, self.outerRelation, self.group)
+    def join(self, pairs=None, capacity=None):
+        """`pairs`: optional device int64 tensor that receives this rank's (rid_R, rid_S) pairs."""
+        join_multi_rank(self.ctx, self.innerRelation, self.outerRelation, self.group, pairs, capacity)
         r = self.ctx.result()
         HashJoin.RESULT_COUNTER = r.matches
         HashJoin.RESULT_CHECKSUM = (r.sum_key, r.sum_rid_r, r.sum_rid_s, r.sum_mix)

@@ -46,6 +46,11 @@ def _worker(rank, world, port, per, knobs, out_dir):
     ro = rhj.Relation.from_numpy(outer[rank], per * world, device=rank)
     hj = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=rank, window_caps=(per * world, per * world))
     res = [hj.join().astuple() for _ in range(2)]  # twice: windows are reused
+    # third time with the output materialised: same result, pairs of this rank
+    pairs = torch.full((2 * (res[0][0] + 8),), -1, dtype=torch.int64, device=f"cuda:{rank}")
+    assert hj.join(pairs=pairs).astuple() == res[0]
+    np.save(os.path.join(out_dir, f"pairs{rank}.npy"), pairs.cpu().numpy().view(np.uint64)[: 2 * res[0][0]].reshape(-1, 2))
+    assert int((pairs[2 * res[0][0]:] != -1).sum()) == 0
     np.save(os.path.join(out_dir, f"rank{rank}.npy"), np.array(res, dtype=np.uint64))
     # per-rank histogram getters must agree with the all-gathered view
     np.save(os.path.join(out_dir, f"ghist{rank}.npy"), hj.ctx.get_global_histogram(0))
@@ -64,9 +69,11 @@ def test_two_gpus_nccl_ipc(oracle, tmp_path, knobs):
     mp.spawn(_worker, args=(world, _free_port(), per, knobs, str(tmp_path)), nprocs=world, join=True)
     cfg = oracle.Config(*knobs)
     inner, outer = oracle.generate_reference(world, per, per)
-    want = oracle.join(inner, outer, cfg)
+    want, want_pairs = oracle.join_pairs(inner, outer, cfg, world * per)
     glob = sum(oracle.local_histogram(t, cfg) for t in inner)
     for r in range(world):
+        gp, wp = np.load(tmp_path / f"pairs{r}.npy"), want_pairs[r]
+        assert np.array_equal(gp[np.lexsort((gp[:, 1], gp[:, 0]))], wp[np.lexsort((wp[:, 1], wp[:, 0]))])
         got = np.load(tmp_path / f"rank{r}.npy")
         for rep in range(2):
             assert tuple(int(x) for x in got[rep]) == want[r].astuple()
