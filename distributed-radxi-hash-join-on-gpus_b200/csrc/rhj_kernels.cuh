@@ -1340,22 +1340,40 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
           m[q] = 0;
           first[q] = 0;
           if (e < s_n) {
-            const uint64_t kpart = v >> a.key_shift;
-            uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
-            while (hit) {
-              const uint64_t r = t[hit - 1];
-              if ((r >> a.key_shift) == kpart) {
-                const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
-                if (m[q] == 0) first[q] = hit;
-                m[q] += 1;
-                item_n += 1;
-                item_kpart += kpart;
-                acc_rr += rid_r;
-                acc_rs += rid_s;
-                acc_mix += mix_triple((kpart << a.net_bits) | partition, rid_r, rid_s);
+            if (KS32) {  // rid = low word, key part = high word
+              const uint32_t vhi = (uint32_t)(v >> 32), vlo = (uint32_t)v;
+              uint32_t hit = bucket[(vhi >> hash_shift32) & hmask];
+              while (hit) {
+                const uint64_t r = t[hit - 1];
+                if ((uint32_t)(r >> 32) == vhi) {
+                  const uint32_t rlo = (uint32_t)r;
+                  if (m[q] == 0) first[q] = hit;
+                  m[q] += 1;
+                  item_kpart += vhi;
+                  acc_rr += rlo;
+                  acc_rs += vlo;
+                  acc_mix += mix_triple(((uint64_t)vhi << a.net_bits) | partition, rlo, vlo);
+                }
+                hit = next[hit - 1];
               }
-              hit = next[hit - 1];
+            } else {
+              const uint64_t kpart = v >> a.key_shift;
+              uint32_t hit = bucket[(uint32_t)(v >> a.shift_bits) & hmask];
+              while (hit) {
+                const uint64_t r = t[hit - 1];
+                if ((r >> a.key_shift) == kpart) {
+                  const uint64_t rid_r = r & rid_mask, rid_s = v & rid_mask;
+                  if (m[q] == 0) first[q] = hit;
+                  m[q] += 1;
+                  item_kpart += kpart;
+                  acc_rr += rid_r;
+                  acc_rs += rid_s;
+                  acc_mix += mix_triple((kpart << a.net_bits) | partition, rid_r, rid_s);
+                }
+                hit = next[hit - 1];
+              }
             }
+            item_n += m[q];
           }
         }
         uint32_t off[NQ], wtot = 0;

@@ -5,8 +5,9 @@ hpcjoin::operators::HashJoin (operators/HashJoin.h:23-43); the phases run in the
 order of operators/HashJoin.cpp:45-220, each phase one call through the C ABI.
 With more than one rank (one process per GPU, torch.distributed/NCCL) the only
 communication is: one all-gather of the per-rank histograms (replaces
-MPI_Allreduce + MPI_Exscan), the peer stores issued by the scatter kernel itself
-(replace MPI_Put) and one barrier (operators/HashJoin.cpp:119-121).
+MPI_Allreduce + MPI_Exscan), the library's own peer stores into the other ranks'
+receive windows (replace MPI_Put) and, per relation, one barrier once every
+rank's stores have landed (operators/HashJoin.cpp:119-121).
 """
 from __future__ import annotations
 
