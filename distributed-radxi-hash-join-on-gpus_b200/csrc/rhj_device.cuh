@@ -160,6 +160,30 @@ __device__ __forceinline__ uint32_t warp_upper_bound(const T *a, uint32_t n, T x
 // completion on an mbarrier, so the load latency is off the consumers' critical path.
 namespace rhj {
 
+// Shared-memory loads through an explicit 32-bit shared-window address.  `pin_u32` makes the
+// address opaque to the compiler, which otherwise recomputes the window base (S2UR CgaCtaId,
+// ULEA, ...) in front of every access of a hot loop instead of spending a register on it.
+__device__ __forceinline__ uint32_t pin_u32(uint32_t v) {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+  return r;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+  uint16_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint64_t lds_u64(uint32_t addr) {
+  uint64_t v;
+  asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(addr));
+  return v;
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

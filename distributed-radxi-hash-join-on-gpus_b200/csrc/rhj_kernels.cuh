@@ -1269,12 +1269,17 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
     // ---- probe (BuildProbe.cpp:97-106) ----
     uint32_t item_n = 0;
     uint64_t item_kpart = 0;
+    // shared-window addresses of the table, biased for the 1-based chain indices
+    const uint32_t sa_bucket = pin_u32(smem_u32(bucket));
+    const uint32_t sa_t = pin_u32(smem_u32(t) - 8);
+    const uint32_t sa_next = pin_u32(smem_u32(next) - 2);
     auto probe = [&](uint64_t v) {
       if (KS32) {  // rid = low word, key part = high word
         const uint32_t vhi = (uint32_t)(v >> 32), vlo = (uint32_t)v;
-        uint32_t hit = bucket[(vhi >> hash_shift32) & hmask];
+        uint32_t hit = lds_u32(sa_bucket + ((vhi >> hash_shift32) & hmask) * 4);
         while (hit) {
-          const uint64_t r = t[hit - 1];
+          const uint64_t r = lds_u64(sa_t + hit * 8);
+          const uint32_t nx = lds_u16(sa_next + hit * 2);
           if ((uint32_t)(r >> 32) == vhi) {
             const uint32_t rlo = (uint32_t)r;
             item_n += 1;
@@ -1283,7 +1288,7 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
             acc_rs += vlo;
             acc_mix += mix_triple(((uint64_t)vhi << a.net_bits) | partition, rlo, vlo);
           }
-          hit = next[hit - 1];
+          hit = nx;
         }
       } else {
         const uint64_t kpart = v >> a.key_shift;
@@ -1310,11 +1315,19 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
           for (int u = 0; u < kBp3SV; ++u)
             if (base + 2 * (u * TPB + tid) < s_n) xs_cur[u] = ld_stream_v2(v2 + base / 2 + u * TPB);
         }
+        if (base + BATCH <= s_n) {  // whole batch in range: no per-tuple bounds checks
 #pragma unroll
-        for (int u = 0; u < kBp3SV; ++u) {
-          const uint32_t e = base + 2 * (u * TPB + tid);
-          if (e < s_n) probe(xs_cur[u].x);
-          if (e + 1 < s_n) probe(xs_cur[u].y);
+          for (int u = 0; u < kBp3SV; ++u) {
+            probe(xs_cur[u].x);
+            probe(xs_cur[u].y);
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < kBp3SV; ++u) {
+            const uint32_t e = base + 2 * (u * TPB + tid);
+            if (e < s_n) probe(xs_cur[u].x);
+            if (e + 1 < s_n) probe(xs_cur[u].y);
+          }
         }
       }
     } else {
