@@ -1224,6 +1224,8 @@ __global__ void __launch_bounds__(TPB, 2048 / TPB >= 4 ? 2 : 1) k_build_probe3(c
       const uint32_t bytes = ((r_n + 1) & ~1u) * 8;  // padded slice: even tuple count
       mbar_arrive_expect_tx(&bars[slot], bytes);
       bulk_g2s(tup0 + slot * CAP, a.src[0] + lo.x, bytes, &bars[slot]);
+      // probe batches after the first are loaded right before use: have them in L2 by then
+      if (s_n > (uint32_t)BATCH) prefetch_l2_range(a.src[1] + lo.y + BATCH, (uint64_t)(s_n - BATCH) * 8);
     }
     const ulonglong2 *v2 = reinterpret_cast<const ulonglong2 *>(a.src[1] + lo.y) + tid;
 #pragma unroll
