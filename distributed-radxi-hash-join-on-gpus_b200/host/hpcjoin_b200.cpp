@@ -4,8 +4,15 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <sys/time.h>
+#include <sys/wait.h>
+#include <sched.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <new>
 
 namespace hpcjoin_b200 {
 
@@ -45,6 +52,124 @@ rhj_config Configuration::toConfig(uint32_t flags) {
 // ---- data ---------------------------------------------------------------------------
 namespace data {
 void SingleRank::allgatherHost(const void *send, void *recv, uint64_t bytes) { memcpy(recv, send, bytes); }
+
+// ---- ProcessComm: ranks = forked processes, exchanges through one MAP_SHARED block ----
+namespace {
+constexpr uint64_t kGatherSlot = 1ull << 20;  // bytes per rank in the all-gather area
+constexpr uint64_t kMailbox = 4ull << 20;     // bytes per ordered pair of ranks in exchange()
+struct ControlBlock {
+  std::atomic<uint32_t> arrived;
+  std::atomic<uint32_t> sense;
+  std::atomic<uint32_t> failed;
+};
+struct Mail {
+  std::atomic<uint32_t> full;
+  uint32_t pad[15];
+};
+inline ControlBlock *control(void *shared) { return static_cast<ControlBlock *>(shared); }
+inline Mail *mail(void *shared, uint32_t n, uint32_t from, uint32_t to) {
+  return reinterpret_cast<Mail *>(static_cast<char *>(shared) + 4096) + (uint64_t)from * n + to;
+}
+inline char *gather_area(void *shared, uint32_t n) { return static_cast<char *>(shared) + 4096 + (uint64_t)n * n * sizeof(Mail); }
+inline char *mailbox(void *shared, uint32_t n, uint32_t from, uint32_t to) {
+  return gather_area(shared, n) + (uint64_t)n * kGatherSlot + ((uint64_t)from * n + to) * kMailbox;
+}
+inline uint64_t shared_bytes(uint32_t n) {
+  return 4096 + (uint64_t)n * n * sizeof(Mail) + (uint64_t)n * kGatherSlot + (uint64_t)n * n * kMailbox;
+}
+inline void spin_until(const std::atomic<uint32_t> &flag, uint32_t value, void *shared) {
+  while (flag.load(std::memory_order_acquire) != value) {
+    if (control(shared)->failed.load(std::memory_order_relaxed)) throw Error{RHJ_ERR_STATE, "another rank failed"};
+    sched_yield();
+  }
+}
+}  // namespace
+
+int ProcessComm::run(uint32_t ranks, int (*body)(ProcessComm &, void *), void *arg) {
+  if (ranks < 1 || ranks > 64) throw Error{RHJ_ERR_INVALID, "ranks must be in [1,64]"};
+  void *shared = mmap(nullptr, shared_bytes(ranks), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+  if (shared == MAP_FAILED) throw Error{RHJ_ERR_INVALID, "mmap of the shared control block failed"};
+  new (control(shared)) ControlBlock();
+  for (uint32_t i = 0; i < ranks * ranks; ++i) new (mail(shared, ranks, 0, 0) + i) Mail();
+  fflush(nullptr);
+  std::vector<pid_t> children;
+  uint32_t me = 0;
+  for (uint32_t r = 1; r < ranks; ++r) {
+    pid_t pid = fork();
+    if (pid < 0) throw Error{RHJ_ERR_INVALID, "fork failed"};
+    if (pid == 0) {
+      me = r;
+      children.clear();
+      break;
+    }
+    children.push_back(pid);
+  }
+  int code = 1;
+  try {
+    ProcessComm comm(me, ranks, shared);
+    code = body(comm, arg);
+  } catch (const Error &e) {
+    fprintf(stderr, "rank %u: rhj error %d: %s\n", me, e.code, e.message.c_str());
+    code = 1;
+  }
+  if (code) control(shared)->failed.store(1);
+  fflush(nullptr);
+  if (me != 0) _exit(code);
+  for (pid_t pid : children) {
+    int st = 0;
+    waitpid(pid, &st, 0);
+    const int c = WIFEXITED(st) ? WEXITSTATUS(st) : 1;
+    if (c > code) code = c;
+  }
+  munmap(shared, shared_bytes(ranks));
+  return code;
+}
+
+void ProcessComm::barrier(void *) {  // sense-reversing; the caller has synchronised its GPU work
+  ControlBlock *cb = control(shared);
+  sense ^= 1;
+  if (cb->arrived.fetch_add(1, std::memory_order_acq_rel) + 1 == n) {
+    cb->arrived.store(0, std::memory_order_relaxed);
+    cb->sense.store(sense, std::memory_order_release);
+  } else {
+    spin_until(cb->sense, sense, shared);
+  }
+}
+
+void ProcessComm::allgatherHost(const void *send, void *recv, uint64_t bytes) {
+  if (bytes > kGatherSlot) throw Error{RHJ_ERR_INVALID, "all-gather block larger than the shared slot"};
+  memcpy(gather_area(shared, n) + (uint64_t)me * kGatherSlot, send, bytes);
+  barrier(nullptr);
+  for (uint32_t r = 0; r < n; ++r)
+    memcpy(static_cast<char *>(recv) + (uint64_t)r * bytes, gather_area(shared, n) + (uint64_t)r * kGatherSlot, bytes);
+  barrier(nullptr);
+}
+
+void ProcessComm::allgatherDevice(const void *send_dev, void *recv_dev, uint64_t bytes, void *) {
+  // u64[2][P] per rank: staged through the host (blocking copies are ordered behind the kernels)
+  if (bytes > kGatherSlot) throw Error{RHJ_ERR_INVALID, "all-gather block larger than the shared slot"};
+  check(rhj_memcpy_d2h(gather_area(shared, n) + (uint64_t)me * kGatherSlot, send_dev, bytes));
+  barrier(nullptr);
+  for (uint32_t r = 0; r < n; ++r)
+    check(rhj_memcpy_h2d(static_cast<char *>(recv_dev) + (uint64_t)r * bytes, gather_area(shared, n) + (uint64_t)r * kGatherSlot, bytes));
+  barrier(nullptr);
+}
+
+void ProcessComm::exchange(const void *send, void *recv, uint64_t bytes, uint32_t peer) {
+  // pairwise swap in mailbox-sized pieces; every ordered pair has its own mailbox and flag, both
+  // sides post before they fetch, so the order in which ranks visit their peers cannot deadlock
+  Mail *out = mail(shared, n, me, peer), *in = mail(shared, n, peer, me);
+  for (uint64_t off = 0; off < bytes || off == 0; off += kMailbox) {
+    const uint64_t len = bytes - off < kMailbox ? bytes - off : kMailbox;
+    spin_until(out->full, 0, shared);
+    memcpy(mailbox(shared, n, me, peer), static_cast<const char *>(send) + off, len);
+    out->full.store(1, std::memory_order_release);
+    spin_until(in->full, 1, shared);
+    memcpy(static_cast<char *>(recv) + off, mailbox(shared, n, peer, me), len);
+    in->full.store(0, std::memory_order_release);
+    if (bytes == 0) break;
+  }
+}
 
 Relation::Relation(uint64_t localSize, uint64_t globalSize) : localSize(localSize), globalSize(globalSize), data(nullptr) {
   void *p = nullptr;
@@ -271,6 +396,10 @@ void HashJoin::join() {
   tasks::NetworkPartitioning networkPartitioning(ctx, stream);
   networkPartitioning.execute();
 
+  if (numberOfNodes > 1) {  // MPI_Win_flush_local_all (data/Window.cpp:193-201): my stores have left
+    check(rhj_exchange_sync(ctx, 0));
+    check(rhj_exchange_sync(ctx, 1));
+  }
   comm->barrier(stream);  // operators/HashJoin.cpp:119-121: every put has landed
 
   // two-level off: the pass is a no-op and only queues BuildProbe (HashJoin.cpp:151-156)

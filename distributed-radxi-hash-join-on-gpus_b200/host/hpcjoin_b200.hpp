@@ -54,9 +54,10 @@ struct CompressedTuple {  // data/CompressedTuple.h:14-20
   unsigned long long value;
 };
 
-// Communication needed by Relation::distribute and the multi-rank join; the single-rank
-// implementation is built in, multi-rank launches use the Python launcher (NCCL) or MPI
-// as sketched in INTEGRATION.md.
+// Communication needed by Relation::distribute and the multi-rank join.  Built in: SingleRank, and
+// ProcessComm for the ranks of one node (one forked process per GPU, host-side exchanges through
+// shared memory -- what `mpirun -np N` on one node is to the reference).  Other launches use the
+// Python launcher (NCCL) or MPI as sketched in INTEGRATION.md.
 struct Comm {
   virtual ~Comm() {}
   virtual uint32_t rank() const = 0;
@@ -73,6 +74,27 @@ struct SingleRank : Comm {
   void allgatherDevice(const void *, void *, uint64_t, void *) override {}
   void allgatherHost(const void *send, void *recv, uint64_t bytes) override;
   void barrier(void *) override {}
+};
+
+// N ranks as N processes of this node.  run() maps the shared control block, forks ranks 1..N-1
+// (it must be called before anything initialises CUDA in the calling process), runs `body` in
+// every rank and returns the largest exit code.  The payload of the join never goes through it:
+// only the histogram all-gather (a few KiB), the window handles, barriers, and Relation::distribute.
+class ProcessComm : public Comm {
+ public:
+  static int run(uint32_t ranks, int (*body)(ProcessComm &comm, void *arg), void *arg);
+  uint32_t rank() const override { return me; }
+  uint32_t size() const override { return n; }
+  void exchange(const void *send, void *recv, uint64_t bytes, uint32_t peer) override;
+  void allgatherDevice(const void *send_dev, void *recv_dev, uint64_t bytes_per_rank, void *stream) override;
+  void allgatherHost(const void *send, void *recv, uint64_t bytes_per_rank) override;
+  void barrier(void *stream) override;
+
+ private:
+  ProcessComm(uint32_t me, uint32_t n, void *shared) : me(me), n(n), shared(shared), sense(0) {}
+  uint32_t me, n;
+  void *shared;
+  uint32_t sense;
 };
 
 class Relation {  // data/Relation.h:18-60

@@ -63,3 +63,38 @@ def test_cpp_hashjoin_materialises_pairs(rhj, oracle, knobs, tmp_path):
     assert int(re.search(r"\[RESULTS\] Tuples:\t(\d+)", p.stdout).group(1)) == n
     cnt, _, _, bad = (int(x) for x in re.search(r"\[RESULTS\] Pairs:\t(\d+)\t(\d+)\t(\d+)\t(\d+)", p.stdout).groups())
     assert cnt == 1000 and bad == 0
+
+
+def test_host_mirror_two_ranks_fail_loudly_without_gpu(rhj, tmp_path):
+    """Two forked ranks (data::ProcessComm): both reach rhj_init, both report the missing device, exit code 1."""
+    import torch
+    exe = build_host(rhj)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([exe, "1000", "5", "5", "27", "1", "0", "2"], capture_output=True, text=True, cwd=tmp_path,
+                       timeout=120)
+    assert p.returncode == 1
+    assert p.stderr.count("rhj error -2") >= 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("knobs", [(5, 5, 27, 1), (8, 8, 24, 1)])
+def test_cpp_hashjoin_two_ranks_match_oracle(rhj, oracle, knobs, tmp_path):
+    """rhj_main with 2 ranks = 2 forked processes, one GPU each, as `mpirun -np 2` of the reference:
+    reference generator + distribute on the host, histograms all-gathered through shared memory,
+    windows opened over CUDA IPC.  Per-rank counts and checksums must equal the oracle's."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    exe = build_host(rhj)
+    n = 150000
+    p = subprocess.run([exe, str(n)] + [str(k) for k in knobs] + ["0", "2"], capture_output=True, text=True,
+                       cwd=tmp_path, timeout=300)
+    assert p.returncode == 0, p.stderr
+    counts = [int(x) for x in re.search(r"\[RESULTS\] Tuples:\t(\d+)\t(\d+)", p.stdout).groups()]
+    inner, outer = oracle.generate_reference(2, n, n)
+    want = oracle.join(inner, outer, oracle.Config(*knobs))
+    for r in range(2):
+        chk = tuple(int(x) for x in re.search(rf"\[RESULTS\] Checksum rank {r}:\t(\d+)\t(\d+)\t(\d+)\t(\d+)", p.stdout).groups())
+        assert (counts[r],) + chk == want[r].astuple()
+    assert sum(counts) == 2 * n
