@@ -126,6 +126,7 @@ struct rhj_ctx {
   int tune_scatter = 2;  // 0 legacy, 1 TMA-staged input, 2 offset-driven (default)
   bool tune_legacy_bp = false;
   int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
+  int tune_l2_ahead_net = 2;  // the network pass reads 16-byte tuples: two tiles ahead measured best (three for 8-byte values)
 };
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
@@ -207,7 +208,7 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
     if (!net_fits || !loc_fits) c->tune_scatter = 0;
   }
   if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
-  if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = std::max(0, std::min(32, atoi(e)));
+  if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = c->tune_l2_ahead_net = std::max(0, std::min(32, atoi(e)));
   if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
   if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
   c->staged_exchange = nranks > 1 && !getenv("RHJ_DIRECT_P2P");
@@ -544,7 +545,7 @@ static int launch_scatter3(rhj_ctx *ctx, const Source &src, const Map &cm, uint3
   // reserve_sms: leave some SMs to a concurrently running push kernel (staged exchange)
   uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)((ctx->sm_count - ctx->reserve_sms) * per_sm));
   kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ctx->tiles_per_chunk, chunk_off, tile_off, tile_start, bin_base,
-                                ctx->d_status, ctx->tune_l2_ahead);
+                                ctx->d_status, Source::kDigitFromValue ? ctx->tune_l2_ahead : ctx->tune_l2_ahead_net);
   RHJ_CHECK_LAUNCH("k_scatter3");
   return RHJ_OK;
 }
