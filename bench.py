@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--loc-bits", type=int, default=0, help="local radix bits (0 = by GPU count)")
     ap.add_argument("--agg", action="store_true", help="warp-aggregated histogram atomics")
     ap.add_argument("--build-cap", type=int, default=0, help="build slice capacity (0 = library default)")
+    ap.add_argument("--debug-env", action="store_true", help="let the library read its RHJ_* ablation switches")
     return ap.parse_args()
 
 
@@ -137,17 +138,62 @@ def host_ranks() -> int:
     return r
 
 
-def cpu_baseline_block(per_rank: int = 1 << 22) -> dict:
+def cpu_model() -> str:
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def mem_available_bytes() -> int:
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable"):
+                return int(ln.split()[1]) * 1024
+    except OSError:
+        pass
+    return 0
+
+
+def reference_sample(total_per_relation: int):
+    """(ranks, tuples per rank) for the reference's CPU run of `total_per_relation` x the same:
+    all host cores the reference can use (one single-threaded rank per core, a power of two so
+    that p % n balances the 32 shipped partitions).  The whole relation pair is used unless the
+    host lacks the memory for it (~80 bytes per tuple pair of a rank: relations, pool, windows)."""
     ranks = host_ranks()
+    per = total_per_relation // ranks
+    avail = mem_available_bytes()
+    note = None
+    while avail and per * ranks * 96 > avail * 0.8 and per > (1 << 20):
+        per //= 2
+        note = f"host has {avail >> 30} GiB available: sample reduced to {per * ranks} tuples per relation"
+    return ranks, per, note
+
+
+def cpu_baseline_block(total_per_relation: int) -> dict:
+    """The reference's own CPU code on this box: (1) the bench workload on all host cores,
+    (2) BASELINE configs[0] as stated: 16M x 16M, 2 ranks, two-level partitioning on."""
+    ranks, per_rank, note = reference_sample(total_per_relation)
     try:
         v, info = cpu_reference_run(per_rank, ranks)
-        return {"value": v, "unit": UNIT, "cores": ranks, "kind": "reference",
-                "sample": f"{ranks} ranks x ({per_rank} x {per_rank}) 16-byte tuples, unique keys, reference generator, "
-                          f"two-level on, 5+5 radix bits; JTOTAL max over ranks {info['join_us_max']} us",
-                "host_cpus": os.cpu_count()}
+        block = {"value": v, "unit": UNIT, "cores": ranks, "kind": "reference",
+                 "sample": f"{ranks} ranks x ({per_rank} x {per_rank}) 16-byte tuples = {ranks * per_rank} x {ranks * per_rank}, "
+                           f"unique keys, reference generator + distribute, two-level on, 5+5 radix bits; "
+                           f"JTOTAL max over ranks {info['join_us_max']} us" + (f"; {note}" if note else ""),
+                 "host_cpus": os.cpu_count(), "cpu_model": cpu_model()}
+        try:
+            v1, info1 = cpu_reference_run(1 << 23, 2)
+            block["config1"] = {"value": v1, "unit": UNIT, "cores": 2,
+                                "sample": "BASELINE configs[0]: 16M x 16M 16-byte tuples, 2 ranks x (8M x 8M), unique keys, "
+                                          f"two-level on, 5+5 radix bits; JTOTAL max over ranks {info1['join_us_max']} us"}
+        except Exception as e:
+            block["config1"] = {"unavailable": str(e)[:200]}
+        return block
     except Exception as e:  # the reference binary did not travel / failed: fall back to the oracle port
         from oracle import oracle as O
-        import numpy as np
         n = 1 << 21
         inner, outer = [O.fill_perm(n, 0, n, 1)], [O.fill_perm(n, 0, n, 2)]
         t0 = time.time()
@@ -162,8 +208,10 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    ranks = host_ranks()
-    per_rank = 1 << 22
+    # the GPU arm's N=1 workload (256M x 256M) in full; at N>1 the same 256M x 256M as a bounded
+    # sample of the N x larger global relations, so that K+W runs still end within minutes
+    n_total = 1 << args.log2n
+    ranks, per_rank, note = reference_sample(n_total)
     vals = []
     info = None
     for i in range(args.warmup + args.steps):
@@ -172,17 +220,43 @@ def run_reference_arm(args):
             vals.append(v)
     value = len(vals) / sum(1.0 / v for v in vals)  # harmonic mean == total tuples / total time
     total = 2 * per_rank * ranks
-    sample = (f"{ranks} reference ranks (1 thread each) x ({per_rank} x {per_rank}) 16-byte tuples per rank, unique keys, "
-              f"reference generator + distribute, two-level on, 5+5 radix bits (BASELINE configs[0] knobs)")
+    sample = (f"{ranks} reference ranks (1 thread each) x ({per_rank} x {per_rank}) 16-byte tuples per rank = "
+              f"{ranks * per_rank} x {ranks * per_rank}, unique keys, reference generator + distribute, two-level on, "
+              f"5+5 radix bits (BASELINE configs[0] knobs)" + (f"; {note}" if note else ""))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / value * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "bounded sample of 256M x 256M 16-byte tuples, unique keys, 1:1 FK: " + sample},
+            "config": {"workload": f"{ranks * per_rank} x {ranks * per_rank} 16-byte tuples, unique keys, 1:1 FK "
+                                   f"(BASELINE configs[{1 if args.gpus == 1 else 2}] size{'' if not note else ', reduced'}): " + sample,
+                       "same_size_as_gpu_arm": ranks * per_rank == (1 << args.log2n) * max(1, args.gpus)},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": ranks, "kind": "reference", "sample": sample,
-                             "host_cpus": os.cpu_count()},
+                             "host_cpus": os.cpu_count(), "cpu_model": cpu_model()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def parity_prologue(rhj, torch, dist, rank, world, local_rank, net_bits, loc_bits, per=150000):
+    """Checker use of the oracle outside every timed region: all five result words of THIS rank
+    must equal oracle.join(...)[rank] on the reference generator's relations."""
+    import numpy as np
+    from oracle import oracle as O
+    inner, outer = O.generate_reference(world, per, per)
+    ocfg = O.Config(net_bits, loc_bits, 32 - net_bits, 1)
+    want = O.join(inner, outer, ocfg)[rank].astuple()
+    cfg = rhj.make_config(net_bits, loc_bits, 32 - net_bits, True)
+    ri = rhj.Relation.from_numpy(inner[rank], per * world, device=local_rank)
+    ro = rhj.Relation.from_numpy(outer[rank], per * world, device=local_rank)
+    hj = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=local_rank, window_caps=(per * world, per * world))
+    got = hj.join().astuple()
+    hj.close()
+    ok = torch.tensor([1 if got == want else 0], dtype=torch.int32, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if not int(ok.item()):
+        raise AssertionError(f"rank {rank}: CUDA {got} != oracle {want}")
+    return {"vs": "oracle", "ranks": world, "ok": True, "tuples_per_rank": per,
+            "workload": "reference generator + distribute (main.cpp:94-104)", "words": 5}
 
 
 # ------------------------------------------------------------------------------------
@@ -208,6 +282,7 @@ def run_ours(args):
     n = 1 << args.log2n          # tuples per relation per GPU
     G = n * world                # global relation size
     flags = (rhj.FLAG_HIST_WARP_AGGREGATE if args.agg else 0) | (rhj.FLAG_STAGE_HOST_INPUTS if world == 1 else 0)
+    flags |= rhj.FLAG_DEBUG_ENV if args.debug_env else 0
     # radix bits: sub-partitions of ~4096 build tuples (one shared-memory table) need
     # log2(global size / 4096) bits in total; weak scaling adds log2(N) bits
     default_bits = {1: (8, 8), 2: (8, 9), 4: (9, 9), 8: (9, 10)}.get(world, (9, 10))
@@ -241,15 +316,52 @@ def run_ours(args):
         else:
             rhj.join_multi_rank(ctx, inner, outer)
 
-    def check(res):
-        tot = torch.tensor([res.matches, res.sum_key, res.sum_rid_r, res.sum_rid_s], dtype=torch.int64, device=dev)
+    m64 = (1 << 64) - 1
+
+    def expected_checksum():
+        """(count, sum key, sum rid_R, sum rid_S, sum mix) of the whole job, computed on the device
+        independently of the join: pos[key_R] = rid_R for every inner tuple of every rank, gathered at
+        this rank's outer keys, then the mix term (rhj_device.cuh mix_triple == oracle orc_mix) in
+        wrap-around int64 arithmetic.  All five words are all-reduced over the ranks."""
+        pos = torch.empty(G, dtype=torch.int64, device=dev)
+        for r in range(world):
+            blk = d_inner.clone() if r == rank else torch.empty_like(d_inner)
+            if world > 1:
+                dist.broadcast(blk, src=r)
+            v = blk.view(-1, 2)
+            pos[v[:, 0]] = v[:, 1]
+            del blk, v
+        so = d_outer.view(-1, 2)
+        tot = torch.zeros(5, dtype=torch.int64, device=dev)
+        stepn = 1 << 24
+        lo32 = 0xFFFFFFFF
+        for b in range(0, n, stepn):
+            key, rs = so[b:b + stepn, 0], so[b:b + stepn, 1]
+            rr = pos[key]
+            k32 = (key ^ (key >> 32)) & lo32
+            r32 = (rr ^ (rr >> 32)) & lo32
+            s32 = (rs ^ (rs >> 32)) & lo32
+            mix = (r32 ^ 0x9E3779B9) * (s32 ^ 0x85EBCA6B) + (k32 ^ 0xC2B2AE35) * ((r32 + s32 + 0x27D4EB2F) & lo32)
+            tot += torch.stack([torch.tensor(key.numel(), device=dev), key.sum(), rr.sum(), rs.sum(), mix.sum()])
+        del pos
         if world > 1:
-            dist.all_reduce(tot)  # int64 wrap-around sum
-        m = (1 << 64) - 1
-        got = [int(x) & m for x in tot.tolist()]
-        want_sum = (G * (G - 1) // 2) & m
-        assert got[0] == G, f"matches {got[0]} != {G}"
-        assert got[1] == want_sum and got[2] == want_sum and got[3] == want_sum, f"checksum mismatch {got} vs {want_sum}"
+            dist.all_reduce(tot)  # int64 wrap-around sum == arithmetic modulo 2^64
+        return [int(x) & m64 for x in tot.tolist()]
+
+    want = expected_checksum()
+    closed = (G * (G - 1) // 2) & m64
+    assert want[0] == G and want[1] == closed and want[2] == closed and want[3] == closed, want
+
+    def check(res):
+        tot = torch.tensor([x - (1 << 64) if x >= (1 << 63) else x for x in res.astuple()], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(tot)
+        got = [int(x) & m64 for x in tot.tolist()]
+        assert got == want, f"result {got} != expected {want} (count, sum key, sum rid_R, sum rid_S, sum mix)"
+
+    # untimed prologue: the reference's own workload (main.cpp:94-104 generator + distribute) at
+    # oracle size through the same launcher, every rank against the oracle's per-rank result
+    parity = parity_prologue(rhj, torch, dist, rank, world, local_rank, net_bits, loc_bits)
 
     for _ in range(args.warmup):
         step()
@@ -354,7 +466,7 @@ def run_ours(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline_block()
+        cpu = cpu_baseline_block(n)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -368,7 +480,7 @@ def run_ours(args):
                            "local send buffers pushed with coalesced P2P stores over NVLink (CUDA IPC windows)"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "stages": stages, "cpu_baseline": cpu,
-                "result": {"matches": G, "checksum_ok": True}}
+                "result": {"matches": G, "checksum_ok": True, "checksum_words": 5}, "parity": parity}
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

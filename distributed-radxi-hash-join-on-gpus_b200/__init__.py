@@ -43,6 +43,7 @@ class Config(C.Structure):
 FLAG_HIST_WARP_AGGREGATE = 1
 FLAG_STAGE_HOST_INPUTS = 2
 FLAG_BALANCED_ASSIGNMENT = 4
+FLAG_DEBUG_ENV = 8
 
 
 def make_config(network_fanout_bits=5, local_fanout_bits=5, payload_bits=27, enable_two_level=False,

@@ -122,8 +122,8 @@ struct rhj_ctx {
   bool ev_valid[EV_COUNT] = {};
   double h2d_us = 0;
 
-  // tuning knobs (environment: RHJ_SCATTER=legacy, RHJ_IPT_NET, RHJ_IPT_LOC, RHJ_BP=legacy)
-  int tune_scatter = 2;  // 0 legacy, 1 TMA-staged input, 2 offset-driven (default)
+  // kernel choice and ablation knobs (rhj_init; environment only with RHJ_FLAG_DEBUG_ENV)
+  int tune_scatter = 3;  // 0 first generation, 2 offset-driven tiles, 3 write-combining rings (default)
   bool tune_legacy_bp = false;
   int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
   int tune_l2_ahead_net = 2;  // the network pass reads 16-byte tuples: two tiles ahead measured best (three for 8-byte values)
@@ -196,23 +196,29 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
-  if (const char *e = getenv("RHJ_SCATTER")) c->tune_scatter = strcmp(e, "legacy") == 0 ? 0 : 2;
-  // The offset-driven kernels hold two staged tiles plus three per-bin slot arrays in shared
-  // memory, which stops fitting above 2048 bins; wider fan-outs run on the first-generation pair
+  // Kernel choice by fan-out.  The write-combining scatter keeps one ring per bin in shared memory,
+  // which stops fitting above 1024 bins; wider fan-outs run on the first-generation pair
   // (k_histogram + k_scatter: one staged tile, per-tile scan).
-  {
-    const size_t smem_limit = 227 * 1024;
-    const bool net_fits = (cfg->tuple_bytes == 16 ? scatter3_smem_bytes<InputSource<16>>(c->P)
-                                                  : scatter3_smem_bytes<InputSource<8>>(c->P)) <= smem_limit;
-    const bool loc_fits = !cfg->enable_two_level || scatter3_smem_bytes<ValueSource>(c->L) <= smem_limit;
-    if (!net_fits || !loc_fits) c->tune_scatter = 0;
+  c->tune_scatter = (c->P <= 1024 && (!cfg->enable_two_level || c->L <= 1024)) ? 3 : 0;
+  c->staged_exchange = false;
+  if (cfg->flags & RHJ_FLAG_DEBUG_ENV) {
+    // Ablation switches; only read when the caller asks for them.
+    if (const char *e = getenv("RHJ_SCATTER")) {
+      const int want = strcmp(e, "legacy") == 0 ? 0 : strcmp(e, "tiles") == 0 ? 2 : 3;
+      const size_t smem_limit = 227 * 1024;
+      const bool net_fits = (cfg->tuple_bytes == 16 ? scatter3_smem_bytes<InputSource<16>>(c->P)
+                                                    : scatter3_smem_bytes<InputSource<8>>(c->P)) <= smem_limit;
+      const bool loc_fits = !cfg->enable_two_level || scatter3_smem_bytes<ValueSource>(c->L) <= smem_limit;
+      if (want == 0 || (want == 2 && net_fits && loc_fits)) c->tune_scatter = want;
+    }
+    if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
+    if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = c->tune_l2_ahead_net = std::max(0, std::min(32, atoi(e)));
+    if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
+    if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
+    if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
+    if (getenv("RHJ_STAGED_EXCHANGE")) c->staged_exchange = nranks > 1;
   }
-  if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
-  if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = c->tune_l2_ahead_net = std::max(0, std::min(32, atoi(e)));
-  if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
-  if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
-  c->staged_exchange = nranks > 1 && !getenv("RHJ_DIRECT_P2P");
-  if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
   if (c->staged_exchange) {
     RHJ_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
     for (int k = 0; k < 2; ++k) {
@@ -220,7 +226,6 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
       RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_pushed[k], cudaEventDisableTiming));
     }
   }
-  if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
   *out = c;
   return RHJ_OK;
 }
@@ -302,7 +307,7 @@ static uint64_t default_window_cap(const rhj_config *cfg, uint64_t max_local) {
 }
 
 static void compute_layout(const rhj_config *cfg, int rank, int nranks, const uint64_t max_local[2],
-                           const uint64_t wcap_in[2], Layout *lay) {
+                           const uint64_t wcap_in[2], bool tiles, bool staged, Layout *lay) {
   const uint32_t P = 1u << cfg->network_fanout_bits;
   const uint32_t L = cfg->enable_two_level ? (1u << cfg->local_fanout_bits) : 1u;
   const uint32_t nowned = owned_partitions(P, rank, nranks);
@@ -321,9 +326,11 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
     add((uint64_t)lay->max_chunks1[k] * P * 4);
     if (cfg->enable_two_level) add((uint64_t)lay->max_chunks2[k] * L * 4);
     const uint64_t tpc = chunk / kTile;
-    add((uint64_t)lay->max_chunks1[k] * tpc * P * 4);
-    add((uint64_t)lay->max_chunks1[k] * tpc * P * 2);
-    if (cfg->enable_two_level) {
+    if (tiles) {
+      add((uint64_t)lay->max_chunks1[k] * tpc * P * 4);
+      add((uint64_t)lay->max_chunks1[k] * tpc * P * 2);
+    }
+    if (tiles && cfg->enable_two_level) {
       add((uint64_t)lay->max_chunks2[k] * tpc * L * 4);
       add((uint64_t)lay->max_chunks2[k] * tpc * L * 2);
     }
@@ -339,7 +346,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   add(NS * 8); add((uint64_t)nowned * 8); add(((uint64_t)nowned + 1) * 8);  // item_lstart, jcount, jstart
   add(16); add(5 * 8); add(4);                     // work counter + pair cursor, result, status
   add((NS + kItemSlack) * sizeof(ItemDesc));       // expanded build/probe work list
-  if (nranks > 1) {                                // send buffers + push lists of the staged exchange
+  if (staged) {                                    // send buffers + push lists of the staged exchange
     add(max_local[0] * 8); add(max_local[1] * 8);
     for (int i = 0; i < 3; ++i) add(2ull * P * 8);
   }
@@ -351,7 +358,7 @@ extern "C" uint64_t rhj_workspace_bytes(const rhj_config *cfg, int nranks, uint6
   if (!cfg || validate_config(cfg, 0, nranks)) return 0;
   Layout lay;
   uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
-  compute_layout(cfg, 0, nranks, ml, wc, &lay);  // rank 0 owns the most partitions
+  compute_layout(cfg, 0, nranks, ml, wc, false, false, &lay);  // rank 0 owns the most partitions
   return lay.total;
 }
 
@@ -370,7 +377,8 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   RHJ_CUDA(cudaSetDevice(ctx->device));
   uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
   Layout lay;
-  compute_layout(&ctx->cfg, ctx->rank, ctx->nranks, ml, wc, &lay);
+  const bool tiles = ctx->tune_scatter == 2;
+  compute_layout(&ctx->cfg, ctx->rank, ctx->nranks, ml, wc, tiles, ctx->staged_exchange, &lay);
   for (int k = 0; k < 2; ++k) {
     if (ml[k] >= (1ull << 32) || lay.window_cap[k] >= (1ull << 32))
       return fail(RHJ_ERR_INVALID, "relation %d: per-rank sizes must stay below 2^32 tuples", k);
@@ -400,10 +408,10 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
     if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * P, &ctx->chunk1_hist[k]);
     if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * L, &ctx->chunk2_hist[k]);
     const uint64_t tpc = ctx->tiles_per_chunk;
-    if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_off[k]);
-    if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_start[k]);
-    if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_off[k]);
-    if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_start[k]);
+    if (!rc && tiles) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_off[k]);
+    if (!rc && tiles) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_start[k]);
+    if (!rc && tiles && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_off[k]);
+    if (!rc && tiles && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_start[k]);
   }
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_local_hist);
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_global);
@@ -431,7 +439,7 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (!rc) rc = carve(ctx, 1ull, &ctx->d_status);
   ctx->items_cap = NS + kItemSlack;
   if (!rc) rc = carve(ctx, ctx->items_cap, &ctx->d_items);
-  if (ctx->nranks > 1) {
+  if (ctx->staged_exchange) {
     for (int k = 0; k < 2 && !rc; ++k) rc = carve(ctx, ml[k], &ctx->sendbuf[k]);
     if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_push_src);
     if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_push_dst);
@@ -510,7 +518,7 @@ template <class Source, class Map>
 static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
                             uint32_t *chunk_hist, uint32_t *tile_off, uint16_t *tile_start, cudaStream_t st) {
   if (grid_chunks == 0) return RHJ_OK;
-  if (ctx->tune_scatter == 2) {
+  if (ctx->tune_scatter == 2) {  // offset-driven scatter: per-tile metadata
     // few replicas: every replica has to be summed per tile, and 256 random bins rarely collide
     uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, (256u * ctx->tune_hist_rep) / nbins));
     size_t smem = ((size_t)2 * nbins * nrep + nbins + 80) * 4;
@@ -523,7 +531,7 @@ static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint
   const bool agg = (ctx->cfg.flags & RHJ_FLAG_HIST_WARP_AGGREGATE) != 0;
   uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, 4096 / nbins));
   size_t smem = (size_t)nbins * nrep * 4;
-  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 4);
+  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)std::max(1, ctx->sm_count - ctx->reserve_sms) * 4);
   if (agg)
     k_histogram<Source, Map, true><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, chunk_hist, ctx->d_status);
   else
@@ -550,11 +558,61 @@ static int launch_scatter3(rhj_ctx *ctx, const Source &src, const Map &cm, uint3
   return RHJ_OK;
 }
 
+// Ring geometry of the write-combining scatter for a fan-out: CTA size, tuples per thread and
+// batch, ring size per bin.  Two CTAs per SM where the rings allow it: while one waits at a
+// barrier or for its loads the other one runs.
+struct WcGeometry {
+  int tpb, ipt, cfix;
+  uint32_t ring;
+};
+static bool wc_geometry(uint32_t nbins, WcGeometry *g) {
+  if (nbins > 1024) return false;
+  if (nbins == 1024) *g = {1024, 4, 24, 24};
+  else if (nbins == 512) *g = {512, 4, 24, 24};
+  else if (nbins == 256) *g = {512, 8, 48, 48};
+  else {
+    uint32_t c = 16;
+    while (c * 2 * nbins <= 12288 && c < 2048) c *= 2;  // power of two, at most 96 KB of rings
+    *g = {512, 8, 0, c};
+  }
+  return true;
+}
+
+template <class Source, class Map, int TPB, int IPT, int CFIX>
+static int launch_scatter_wc_t(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+                               uint32_t ring, const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+  const size_t smem = scatter_wc_smem_bytes(nbins, ring, TPB);
+  auto kern = k_scatter_wc<Source, Map, TPB, IPT, CFIX>;
+  RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem));
+  if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
+  per_sm = std::min(per_sm, TPB <= 512 ? 2 : 1);
+  const uint32_t sms = (uint32_t)std::max(1, ctx->sm_count - ctx->reserve_sms);
+  const uint32_t grid = std::min<uint32_t>(grid_chunks, sms * (uint32_t)per_sm);
+  kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ring, chunk_off, bin_base, ctx->d_status,
+                                Source::kDigitFromValue ? ctx->tune_l2_ahead : ctx->tune_l2_ahead_net);
+  RHJ_CHECK_LAUNCH("k_scatter_wc");
+  return RHJ_OK;
+}
+
+template <class Source, class Map>
+static int launch_scatter_wc(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
+                             const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+  WcGeometry g;
+  if (!wc_geometry(nbins, &g)) return fail(RHJ_ERR_INVALID, "no ring geometry for %u bins", nbins);
+  if (g.cfix == 48) return launch_scatter_wc_t<Source, Map, 512, 8, 48>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
+  if (g.cfix == 24 && g.tpb == 512) return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
+  if (g.cfix == 24) return launch_scatter_wc_t<Source, Map, 1024, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
+  return launch_scatter_wc_t<Source, Map, 512, 8, 0>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
+}
+
 template <class Source, class Map>
 static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
                           const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
                           const uint64_t *bin_base, cudaStream_t st) {
   if (grid_chunks == 0) return RHJ_OK;
+  if (ctx->tune_scatter == 3) return launch_scatter_wc(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
   if (ctx->tune_scatter == 2) {
     if (ctx->tune_tpb == 1024)
       return launch_scatter3<Source, Map, 1024>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);

@@ -434,6 +434,278 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
 }
 
 // ---------------------------------------------------------------------------------
+// K2 / K3, write-combining: the reference's software write-combining buffers
+// (cacheline_t, tasks/NetworkPartitioning.cpp:28-40, 138-141, remainders :186-209;
+// tasks/LocalPartitioning.cpp:194-250) restated for an SM.  Every bin owns a small ring
+// of C tuples in shared memory.  A tuple takes the next position q of its bin with one
+// shared atomic; position q of bin d belongs at byte address base[d] + 8 q, and base[d]
+// is 128-byte aligned, so q % 16 == 0 is the start of a destination line.  Between two
+// batches of input the warps that own a bin copy every COMPLETE line of it out of the
+// ring with 16-byte stores -- eight lanes per 128-byte line, four lines per store
+// instruction -- and keep the remainder (< 16 tuples) for the next batch.  Only whole,
+// aligned lines leave the SM: no partial sectors for L2 to merge, no read-modify-write
+// in DRAM, and a destination in a peer GPU's window sees full-line NVLink writes.  Heads
+// and tails (partial lines) are written once per bin and CTA, because a CTA works on a
+// CONTIGUOUS run of chunks and the chunk offsets of consecutive chunks are adjacent.
+//
+// One 32-bit word per bin holds the bin's next position (low half) and the first
+// position that no longer fits the ring (high half), so placing a tuple costs a single
+// shared-memory transaction besides the store of the tuple itself.  A tuple that does not
+// fit (a hot bin under skew) goes straight to its final address with an 8-byte store:
+// exact offsets make every position's address known, so overflow needs no second pass.
+// Positions are kept small by moving multiples of the rebase unit from the counters into
+// base[] (the unit is a multiple of the ring size and of a line, so neither ring slots nor
+// line boundaries move): with a compile-time ring size the positions still in the ring are
+// below unit + ring, and "position modulo ring size" is one or two conditional subtractions.
+//
+// No per-tile metadata: the histogram pass only has to deliver per-chunk offsets.
+//   bin_base  [nsegs][nbins] u64: byte address of this rank's first slot of (seg, bin)
+//   chunk_off [chunk][nbins] u32: exclusive per-chunk offsets from k_colscan (tuples)
+// ---------------------------------------------------------------------------------
+constexpr uint32_t kWcListCap = 128;      // line items per warp and round
+constexpr uint32_t kWcLinesPerRound = 4;  // lines one bin contributes per round (32 * 4 = kWcListCap)
+
+template <int CFIX>
+__host__ __device__ constexpr uint32_t wc_rebase() { return CFIX == 0 ? 16384u : (CFIX % 16 == 0 ? (uint32_t)CFIX : 2u * CFIX); }
+
+__host__ __device__ inline size_t scatter_wc_smem_bytes(uint32_t nbins, uint32_t ring, uint32_t tpb) {
+  return (size_t)nbins * ring * 8 + (size_t)nbins * (8 + 4 + 2) + (size_t)(tpb / 32) * kWcListCap * 4 + 16;
+}
+
+__device__ __forceinline__ void st_stream_v2(void *p, const ulonglong2 &v) {
+  asm volatile("st.global.L1::no_allocate.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v.x), "l"(v.y) : "memory");
+}
+// shared-memory accesses through pinned 32-bit shared-window addresses (see pin_u32)
+__device__ __forceinline__ uint32_t atoms_inc(uint32_t addr) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr) : "memory");
+  return old;
+}
+__device__ __forceinline__ void sts_u64(uint32_t addr, uint64_t v) {
+  asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ ulonglong2 lds_v2(uint32_t addr) {
+  ulonglong2 v;
+  asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr));
+  return v;
+}
+
+// CFIX: ring size as a compile-time constant (24 or 48 tuples), or 0 = a power of two given at run time
+template <class Source, class Map, int TPB, int IPT, int CFIX>
+__global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
+    k_scatter_wc(const Source src, const Map cm, const uint32_t nbins, const uint32_t ring_tuples,
+                 const uint32_t *__restrict__ chunk_off, const uint64_t *__restrict__ bin_base,
+                 const int *__restrict__ status, const int l2_ahead) {
+  using Raw = typename Source::Raw;
+  constexpr uint32_t BATCH = TPB * IPT, NW = TPB / 32, M = wc_rebase<CFIX>();
+  constexpr uint32_t FULL = 0xFFFFFFFFu;
+  extern __shared__ __align__(128) unsigned char sh_raw[];
+  if (*status != kDevOk) return;
+  const uint32_t C = CFIX ? (uint32_t)CFIX : ring_tuples;
+  uint64_t *const ring = reinterpret_cast<uint64_t *>(sh_raw);      // [nbins][C]
+  uint64_t *const base = ring + (size_t)nbins * C;                  // [nbins] line-aligned byte address of position 0
+  uint32_t *const word = reinterpret_cast<uint32_t *>(base + nbins);  // [nbins] (limit << 16) | next position
+  uint32_t *const list = word + nbins;                              // [NW][kWcListCap]
+  uint16_t *const head = reinterpret_cast<uint16_t *>(list + NW * kWcListCap);  // [nbins] first position still in the ring
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t cmask = C - 1;
+  // ring slot of a position that is still in the ring (q < rebase unit + ring size when CFIX != 0)
+  auto slot = [&](uint32_t q) -> uint32_t {
+    if (CFIX == 0) return q & cmask;
+    if (q >= (uint32_t)CFIX) q -= CFIX;
+    if (M > (uint32_t)CFIX && q >= (uint32_t)CFIX) q -= CFIX;
+    return q;
+  };
+  const uint32_t sa_ring = pin_u32(smem_u32(ring)), sa_word = pin_u32(smem_u32(word));
+
+  const uint32_t nchunks = cm.count();
+  const uint32_t c_begin = (uint32_t)((uint64_t)blockIdx.x * nchunks / gridDim.x);
+  const uint32_t c_end = (uint32_t)((uint64_t)(blockIdx.x + 1) * nchunks / gridDim.x);
+  if (c_begin >= c_end) return;
+  for (uint32_t d = tid; d < nbins; d += TPB) {
+    word[d] = 0;
+    head[d] = 0;
+    base[d] = 0;
+  }
+
+  // Copy the complete lines of every bin out of the rings (mode 0); at the start of chunk c
+  // also bind bins whose destination does not continue where they stand (mode 1: their
+  // remainder goes out as a partial line first); mode 2 empties everything.
+  // Runs between two barriers: nobody places tuples meanwhile.
+  auto flush = [&](const int mode, const uint32_t c, const uint32_t seg) {
+    const uint32_t bpw = nbins >= NW ? nbins / NW : 1u;
+    const uint32_t first = warp * bpw;
+    uint32_t *const mylist = list + warp * kWcListCap;
+    for (uint32_t g0 = 0; g0 < bpw; g0 += 32) {
+      const uint32_t idx = g0 + lane, bin = first + idx;
+      const bool valid = idx < bpw && bin < nbins;
+      uint32_t t = 0, fa = 0, fb = 0, nh = 0, nl = 0, line0 = 0;
+      uint64_t b = 0;
+      if (valid) {
+        const uint32_t w32 = word[bin];
+        t = w32 & 0xFFFFu;
+        const uint32_t lim = w32 >> 16;
+        const uint32_t h = head[bin];
+        b = base[bin];
+        bool all = mode == 2 || t >= lim;
+        bool rebind = false;
+        uint64_t new_addr = 0;
+        if (mode == 1) {
+          new_addr = bin_base[(size_t)seg * nbins + bin] + (uint64_t)chunk_off[(size_t)c * nbins + bin] * 8;
+          rebind = new_addr != b + (uint64_t)t * 8;
+          all = all || rebind;
+        }
+        fa = h;
+        if (all) {
+          fb = t < lim ? t : lim;  // what the ring holds; later positions went straight to memory
+          nh = t;
+        } else {
+          const uint32_t e = t & ~15u;
+          fb = e > h ? e : h;
+          nh = fb;
+        }
+        if (fb > fa) {
+          line0 = fa & ~15u;
+          nl = (fb + 15 - line0) >> 4;
+        }
+        if (rebind) {  // applied when the state is written back below
+          b = new_addr & ~uint64_t(127);
+          t = nh = (uint32_t)(new_addr >> 3) & 15u;
+        }
+      }
+      const uint32_t range = fa | (fb << 16);
+      uint32_t done = 0;
+      while (__any_sync(FULL, nl > done)) {
+        const uint32_t k = nl > done ? min(nl - done, kWcLinesPerRound) : 0u;
+        const uint32_t incl = warp_inclusive_scan(k);
+        const uint32_t total = __shfl_sync(FULL, incl, 31);
+        for (uint32_t j = 0; j < k; ++j) mylist[incl - k + j] = (lane << 16) | (line0 + (done + j) * 16);
+        __syncwarp();
+        for (uint32_t i0 = 0; i0 < total; i0 += 4) {
+          const uint32_t i = i0 + (lane >> 3);
+          const uint32_t ent = i < total ? mylist[i] : 0u;
+          const uint32_t owner = ent >> 16, ql = ent & 0xFFFFu;
+          const uint32_t r = __shfl_sync(FULL, range, owner);
+          if (i < total) {
+            const uint32_t fa_i = r & 0xFFFFu, fb_i = r >> 16;
+            const uint32_t bin_i = first + g0 + owner;
+            const uint64_t b_i = base[bin_i];  // still the value the positions in the ring refer to
+            const uint32_t q0 = ql + 2 * (lane & 7);
+            const uint64_t *const rp = ring + (size_t)bin_i * C;
+            if (fa_i <= ql && ql + 16 <= fb_i) {
+              const ulonglong2 v = lds_v2(sa_ring + (bin_i * C + slot(q0)) * 8);
+              st_stream_v2(reinterpret_cast<void *>(b_i + (uint64_t)q0 * 8), v);
+            } else {
+              if (fa_i <= q0 && q0 < fb_i)
+                st_stream_u64(reinterpret_cast<uint64_t *>(b_i + (uint64_t)q0 * 8), rp[slot(q0)]);
+              if (fa_i <= q0 + 1 && q0 + 1 < fb_i)
+                st_stream_u64(reinterpret_cast<uint64_t *>(b_i + (uint64_t)(q0 + 1) * 8), rp[slot(q0 + 1)]);
+            }
+          }
+        }
+        __syncwarp();
+        done += k;
+      }
+      if (valid) {
+        if (nh >= M) {
+          const uint32_t k = (nh / M) * M;
+          nh -= k;
+          t -= k;
+          b += (uint64_t)k * 8;
+        }
+        const uint32_t lim = (nh & ~15u) + C;
+        word[bin] = (lim << 16) | t;
+        head[bin] = (uint16_t)nh;
+        base[bin] = b;
+      }
+    }
+  };
+
+  auto load_raw = [&](const Raw *p, uint32_t n, Raw (&raw)[IPT]) {
+    p += tid;
+    if (n >= BATCH) {
+#pragma unroll
+      for (int u = 0; u < IPT; ++u) raw[u] = ld_stream(p + u * TPB);
+    } else {
+#pragma unroll
+      for (int u = 0; u < IPT; ++u)
+        if (u * TPB + tid < n) raw[u] = ld_stream(p + u * TPB);
+    }
+  };
+  auto put = [&](uint64_t v, uint32_t d, uint32_t w32) {
+    const uint32_t q = w32 & 0xFFFFu;
+    if (__builtin_expect(q < (w32 >> 16), 1)) sts_u64(sa_ring + (d * C + slot(q)) * 8, v);
+    else st_stream_u64(reinterpret_cast<uint64_t *>(base[d] + (uint64_t)q * 8), v);
+  };
+  auto place = [&](const Raw (&raw)[IPT], uint32_t n) {
+    constexpr int G = IPT < 4 ? IPT : 4;  // atomics in flight per thread
+    if (n >= BATCH) {
+#pragma unroll
+      for (int u0 = 0; u0 < IPT; u0 += G) {
+        uint64_t v[G];
+        uint32_t d[G], w[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          src.decode(raw[u0 + g], v[g], d[g]);
+          w[g] = atoms_inc(sa_word + d[g] * 4);
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) put(v[g], d[g], w[g]);
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < IPT; ++u) {
+        if (u * TPB + tid < n) {
+          uint64_t v;
+          uint32_t d;
+          src.decode(raw[u], v, d);
+          put(v, d, atoms_inc(sa_word + d * 4));
+        }
+      }
+    }
+  };
+
+  const Raw *const in0 = static_cast<const Raw *>(src.base());
+  uint64_t cb, ce;
+  uint32_t seg;
+  cm.range(c_end - 1, cb, ce, seg);
+  const uint64_t in_end = ce;  // the chunks of one CTA are contiguous in the input
+  uint32_t c = c_begin;
+  cm.range(c, cb, ce, seg);
+  uint64_t pos = cb;
+  Raw raw[IPT];
+  load_raw(in0 + pos, (uint32_t)min((uint64_t)BATCH, ce - pos), raw);
+  if (tid == 0)
+    for (int a = 1; a <= l2_ahead; ++a) {
+      const uint64_t p = pos + (uint64_t)a * BATCH;
+      if (p < in_end) prefetch_l2_range(in0 + p, min((uint64_t)BATCH, in_end - p) * sizeof(Raw));
+    }
+  bool chunk_start = true;
+  while (true) {
+    const uint32_t n = (uint32_t)min((uint64_t)BATCH, ce - pos);
+    __syncthreads();
+    flush(chunk_start ? 1 : 0, c, seg);
+    __syncthreads();
+    place(raw, n);
+    pos += n;
+    chunk_start = false;
+    if (pos >= ce) {
+      if (++c >= c_end) break;
+      cm.range(c, cb, ce, seg);
+      pos = cb;
+      chunk_start = true;
+    }
+    load_raw(in0 + pos, (uint32_t)min((uint64_t)BATCH, ce - pos), raw);
+    if (tid == 0 && l2_ahead > 0) {
+      const uint64_t p = pos + (uint64_t)l2_ahead * BATCH;
+      if (p < in_end) prefetch_l2_range(in0 + p, min((uint64_t)BATCH, in_end - p) * sizeof(Raw));
+    }
+  }
+  __syncthreads();
+  flush(2, 0, 0);
+}
+
+// ---------------------------------------------------------------------------------
 // Ks: column-wise exclusive scan of a [rows][ncols] u32 matrix, per row segment.
 // grid = (ceil(ncols/32), nsegs); block = WARPS*32.  Lane = column (coalesced rows),
 // warps split the segment's rows; three phases: partial column sums, scan across

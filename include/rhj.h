@@ -53,7 +53,8 @@ typedef struct rhj_config {
   uint32_t flags;               /* RHJ_FLAG_* */
 } rhj_config;
 
-#define RHJ_FLAG_HIST_WARP_AGGREGATE 1u /* warp-aggregate the histogram atomics (skew-proof) */
+#define RHJ_FLAG_HIST_WARP_AGGREGATE 1u /* merge equal digits inside a warp before the shared-memory atomic (one hot key costs
+                                           one atomic per warp instead of 32); slower on uniform data */
 #define RHJ_FLAG_STAGE_HOST_INPUTS 2u    /* rhj_plan also reserves device staging for rhj_join_host */
 /* Size-balanced partition -> rank assignment instead of AssignmentMap.cpp:41-43's p % n (which
  * receives the histograms but ignores them).  Rule, identical on every rank:
@@ -63,6 +64,9 @@ typedef struct rhj_config {
  * keep the reference's definition (OffsetMap.cpp:59-93) under the new owners.  All ranks of a join
  * must set the flag alike. */
 #define RHJ_FLAG_BALANCED_ASSIGNMENT 4u
+/* Development only: rhj_init also reads the RHJ_* ablation switches from the environment
+ * (DESIGN.md section 4).  Without this flag the library never calls getenv. */
+#define RHJ_FLAG_DEBUG_ENV 8u
 
 /* Join result: the reference only counts (HashJoin::RESULT_COUNTER, operators/HashJoin.cpp:28,
  * tasks/BuildProbe.cpp:97-115).  The sums are an order-independent checksum over
