@@ -63,7 +63,8 @@ class Result(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [("jtotal_us", C.c_double), ("jhist_us", C.c_double), ("jmpi_us", C.c_double),
-                ("jproc_us", C.c_double), ("lp_us", C.c_double), ("bp_us", C.c_double), ("h2d_us", C.c_double)]
+                ("jproc_us", C.c_double), ("lp_us", C.c_double), ("bp_us", C.c_double), ("h2d_us", C.c_double),
+                ("snetcompl_us", C.c_double)]
 
     def asdict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -102,6 +103,8 @@ SYMBOLS = {
     "rhj_get_base_offsets": (_int, [_vp, _int, _vp, _vp]),
     "rhj_get_write_offsets": (_int, [_vp, _int, _vp, _vp]),
     "rhj_network_partition": (_int, [_vp, _vp]),
+    "rhj_network_partition_rel": (_int, [_vp, _int, _vp]),
+    "rhj_set_sm_limit": (_int, [_vp, _int]),
     "rhj_local_partition": (_int, [_vp, _vp]),
     "rhj_exchange_wait": (_int, [_vp, _int, _vp]),
     "rhj_exchange_sync": (_int, [_vp, _int]),
@@ -249,6 +252,12 @@ class Context:
 
     def network_partition(self):
         check(lib().rhj_network_partition(self.h, _stream()))
+
+    def network_partition_rel(self, which: int):
+        check(lib().rhj_network_partition_rel(self.h, which, _stream()))
+
+    def set_sm_limit(self, sms: int):
+        check(lib().rhj_set_sm_limit(self.h, sms))
 
     def local_partition(self):
         check(lib().rhj_local_partition(self.h, _stream()))

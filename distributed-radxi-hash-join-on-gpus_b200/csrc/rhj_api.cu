@@ -104,7 +104,9 @@ struct rhj_ctx {
   uint64_t *d_push_src = nullptr, *d_push_dst = nullptr, *d_push_cnt = nullptr;
   cudaStream_t side = nullptr;
   cudaEvent_t ev_scattered[2] = {nullptr, nullptr}, ev_pushed[2] = {nullptr, nullptr};
-  bool rel_partitioned[2] = {false, false};
+  bool rel_partitioned[2] = {false, false}, rel_scattered[2] = {false, false}, wait_timed[2] = {false, false};
+  cudaEvent_t ev_rel_net[2] = {nullptr, nullptr}, ev_rel_local[2] = {nullptr, nullptr};
+  cudaEvent_t ev_wait0[2] = {nullptr, nullptr}, ev_wait1[2] = {nullptr, nullptr};
   bool staged_exchange = false;
   int reserve_sms = 0, tune_push_sms = 32;
 
@@ -126,6 +128,8 @@ struct rhj_ctx {
   int tune_scatter = 3;  // 0 first generation, 2 offset-driven tiles, 3 write-combining rings (default)
   bool tune_legacy_bp = false;
   int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
+  int tune_wc_variant = 0;
+  int tune_wc_l2_net = 4, tune_wc_l2_loc = 4;  // L2 prefetch distance of the ring scatter, quarter batches
   int tune_l2_ahead_net = 2;  // the network pass reads 16-byte tuples: two tiles ahead measured best (three for 8-byte values)
 };
 
@@ -196,6 +200,12 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < EV_COUNT; ++i) RHJ_CUDA(cudaEventCreate(&c->ev[i]));
+  for (int k = 0; k < 2; ++k) {
+    RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_rel_net[k], cudaEventDisableTiming));
+    RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_rel_local[k], cudaEventDisableTiming));
+    RHJ_CUDA(cudaEventCreate(&c->ev_wait0[k]));
+    RHJ_CUDA(cudaEventCreate(&c->ev_wait1[k]));
+  }
   // Kernel choice by fan-out.  The write-combining scatter keeps one ring per bin in shared memory,
   // which stops fitting above 1024 bins; wider fan-outs run on the first-generation pair
   // (k_histogram + k_scatter: one staged tile, per-tile scan).
@@ -218,6 +228,9 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
     if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
     if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
     if (getenv("RHJ_STAGED_EXCHANGE")) c->staged_exchange = nranks > 1;
+    if (const char *e = getenv("RHJ_WC")) c->tune_wc_variant = atoi(e);
+    if (const char *e = getenv("RHJ_WC_L2_NET")) c->tune_wc_l2_net = std::max(0, std::min(64, atoi(e)));
+    if (const char *e = getenv("RHJ_WC_L2_LOC")) c->tune_wc_l2_loc = std::max(0, std::min(64, atoi(e)));
   }
   if (c->staged_exchange) {
     RHJ_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
@@ -250,6 +263,10 @@ extern "C" int rhj_destroy(rhj_ctx *ctx) {
   for (int i = 0; i < EV_COUNT; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   for (int k = 0; k < 2; ++k) {
+    if (ctx->ev_rel_net[k]) cudaEventDestroy(ctx->ev_rel_net[k]);
+    if (ctx->ev_rel_local[k]) cudaEventDestroy(ctx->ev_rel_local[k]);
+    if (ctx->ev_wait0[k]) cudaEventDestroy(ctx->ev_wait0[k]);
+    if (ctx->ev_wait1[k]) cudaEventDestroy(ctx->ev_wait1[k]);
     if (ctx->ev_scattered[k]) cudaEventDestroy(ctx->ev_scattered[k]);
     if (ctx->ev_pushed[k]) cudaEventDestroy(ctx->ev_pushed[k]);
   }
@@ -587,11 +604,11 @@ static int launch_scatter_wc_t(rhj_ctx *ctx, const Source &src, const Map &cm, u
   int per_sm = 0;
   RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem));
   if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
-  per_sm = std::min(per_sm, TPB <= 512 ? 2 : 1);
+  per_sm = std::min(per_sm, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1);
   const uint32_t sms = (uint32_t)std::max(1, ctx->sm_count - ctx->reserve_sms);
   const uint32_t grid = std::min<uint32_t>(grid_chunks, sms * (uint32_t)per_sm);
   kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ring, chunk_off, bin_base, ctx->d_status,
-                                Source::kDigitFromValue ? ctx->tune_l2_ahead : ctx->tune_l2_ahead_net);
+                                Source::kDigitFromValue ? ctx->tune_wc_l2_loc : ctx->tune_wc_l2_net);
   RHJ_CHECK_LAUNCH("k_scatter_wc");
   return RHJ_OK;
 }
@@ -601,6 +618,20 @@ static int launch_scatter_wc(rhj_ctx *ctx, const Source &src, const Map &cm, uin
                              const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
   WcGeometry g;
   if (!wc_geometry(nbins, &g)) return fail(RHJ_ERR_INVALID, "no ring geometry for %u bins", nbins);
+#ifdef RHJ_TUNE_VARIANTS
+  // experiment builds only: RHJ_WC=<variant> picks another geometry for <= 256 bins
+  if (nbins <= 256 && ctx->tune_wc_variant) {
+    const uint32_t r32 = 32;
+    switch (ctx->tune_wc_variant) {
+      case 1: return launch_scatter_wc_t<Source, Map, 256, 8, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st);
+      case 2: return launch_scatter_wc_t<Source, Map, 256, 8, 0>(ctx, src, cm, grid_chunks, nbins, r32, chunk_off, bin_base, st);
+      case 3: return launch_scatter_wc_t<Source, Map, 1024, 8, 96>(ctx, src, cm, grid_chunks, nbins, 96, chunk_off, bin_base, st);
+      case 4: return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st);
+      case 5: return launch_scatter_wc_t<Source, Map, 256, 4, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st);
+      default: break;
+    }
+  }
+#endif
   if (g.cfix == 48) return launch_scatter_wc_t<Source, Map, 512, 8, 48>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
   if (g.cfix == 24 && g.tpb == 512) return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
   if (g.cfix == 24) return launch_scatter_wc_t<Source, Map, 1024, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
@@ -661,7 +692,7 @@ extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner
   ctx->input_n[1] = outer_n;
   for (int k = 0; k < 2; ++k) ctx->nchunks1[k] = (uint32_t)((ctx->input_n[k] + ctx->chunk1 - 1) / ctx->chunk1);
   ctx->local_planned = false;
-  ctx->rel_partitioned[0] = ctx->rel_partitioned[1] = false;
+  for (int k = 0; k < 2; ++k) ctx->rel_partitioned[k] = ctx->rel_scattered[k] = ctx->wait_timed[k] = false;
   int rc = record(ctx, EV_START, st);
   if (rc) return rc;
   RHJ_CUDA(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), st));
@@ -721,42 +752,65 @@ extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, v
   return RHJ_OK;
 }
 
-extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
+// One relation of the network pass.  Direct exchange (default): the scatter kernel's full-line
+// stores go straight into the owner's window, local or peer (MPI_Put, data/Window.cpp:108-115).
+extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
-  if (ctx->stage < 2) return fail(RHJ_ERR_STATE, "rhj_compute_offsets first");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (!ctx->planned || ctx->stage < 2) return fail(RHJ_ERR_STATE, "rhj_compute_offsets first");
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  for (int k = 0; k < 2; ++k) {
-    ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
-    int rc;
-    // while the outer relation is scattered, the inner relation's push runs on the SMs left free
-    ctx->reserve_sms = (ctx->staged_exchange && k == 1) ? ctx->tune_push_sms : 0;
-    if (ctx->cfg.tuple_bytes == 16) {
-      InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
-    } else {
-      InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
-    }
-    if (rc) return rc;
-    if (ctx->staged_exchange) {
-      // push this relation's remote partitions on the side stream: the inner relation's push
-      // overlaps the scatter of the outer relation, the outer relation's push overlaps the
-      // local pass of the inner one (rhj_exchange_wait / rhj_local_partition_rel order the rest)
-      RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
-      RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
-      const uint32_t push_ctas = (uint32_t)std::max(8, ctx->tune_push_sms * 8);
-      k_push<<<push_ctas, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P,
-                                                    ctx->d_push_dst + (uint64_t)k * ctx->P,
-                                                    ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->P, ctx->d_status);
-      RHJ_CHECK_LAUNCH("k_push");
-      RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
-    }
+  const int k = which;
+  ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
+  int rc;
+  const int saved_reserve = ctx->reserve_sms;
+  // staged exchange: while the outer relation is scattered, the inner relation's push runs on the SMs left free
+  if (ctx->staged_exchange && k == 1) ctx->reserve_sms = std::max(ctx->reserve_sms, ctx->tune_push_sms);
+  if (ctx->cfg.tuple_bytes == 16) {
+    InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+    rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
+  } else {
+    InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+    rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
   }
-  ctx->reserve_sms = 0;
-  int rc = record(ctx, EV_NET, st);
+  ctx->reserve_sms = saved_reserve;
   if (rc) return rc;
-  ctx->stage = 3;
+  if (ctx->staged_exchange) {
+    // push this relation's remote partitions on the side stream: the inner relation's push
+    // overlaps the scatter of the outer relation, the outer relation's push overlaps the
+    // local pass of the inner one (rhj_exchange_wait / rhj_local_partition_rel order the rest)
+    RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
+    RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
+    const uint32_t push_ctas = (uint32_t)std::max(8, ctx->tune_push_sms * 8);
+    k_push<<<push_ctas, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P,
+                                                  ctx->d_push_dst + (uint64_t)k * ctx->P,
+                                                  ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->P, ctx->d_status);
+    RHJ_CHECK_LAUNCH("k_push");
+    RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
+  }
+  RHJ_CUDA(cudaEventRecord(ctx->ev_rel_net[k], st));
+  ctx->rel_scattered[k] = true;
+  if (ctx->rel_scattered[k ^ 1]) {
+    rc = record(ctx, EV_NET, st);
+    if (rc) return rc;
+    ctx->stage = 3;
+  }
+  return RHJ_OK;
+}
+
+extern "C" int rhj_network_partition(rhj_ctx *ctx, void *stream) {
+  int rc = rhj_network_partition_rel(ctx, 0, stream);
+  if (!rc) rc = rhj_network_partition_rel(ctx, 1, stream);
+  return rc;
+}
+
+// SMs the kernels launched from now on may occupy (0 = all): lets a launcher run two stages side
+// by side on different streams, e.g. the outer relation's NVLink-bound network pass next to the
+// inner relation's HBM-bound local pass.
+extern "C" int rhj_set_sm_limit(rhj_ctx *ctx, int sms) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (sms < 0) return fail(RHJ_ERR_INVALID, "sms must be >= 0");
+  ctx->reserve_sms = (sms == 0 || sms >= ctx->sm_count) ? 0 : ctx->sm_count - sms;
   return RHJ_OK;
 }
 
@@ -802,11 +856,14 @@ static int launch_plan_local(rhj_ctx *ctx, int k_begin, int k_end, bool do_items
 extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
-  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
-  if (ctx->staged_exchange) {
-    RHJ_CUDA(cudaSetDevice(ctx->device));
-    RHJ_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), ctx->ev_pushed[which], 0));
-  }
+  if (!ctx->rel_scattered[which]) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // `stream` may be another one than the network pass ran on
+  RHJ_CUDA(cudaStreamWaitEvent(st, ctx->staged_exchange ? ctx->ev_pushed[which] : ctx->ev_rel_net[which], 0));
+  // SNETCOMPL (performance/Measurements.cpp:157-165): from here to the start of the local pass
+  RHJ_CUDA(cudaEventRecord(ctx->ev_wait0[which], st));
+  ctx->wait_timed[which] = true;
   return RHJ_OK;
 }
 
@@ -814,27 +871,31 @@ extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
 extern "C" int rhj_exchange_sync(rhj_ctx *ctx, int which) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
-  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  if (!ctx->rel_scattered[which]) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
   RHJ_CUDA(cudaSetDevice(ctx->device));
-  if (ctx->staged_exchange) RHJ_CUDA(cudaEventSynchronize(ctx->ev_pushed[which]));
-  else RHJ_CUDA(cudaEventSynchronize(ctx->ev[EV_NET]));
+  RHJ_CUDA(cudaEventSynchronize(ctx->staged_exchange ? ctx->ev_pushed[which] : ctx->ev_rel_net[which]));
   return RHJ_OK;
 }
 
 extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
-  if (ctx->stage < 3) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
+  if (!ctx->rel_scattered[which]) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc = rhj_exchange_wait(ctx, which, stream);  // this rank's own pushes of the relation are done
-  if (rc) return rc;
+  int rc = RHJ_OK;
+  if (!ctx->wait_timed[which]) {
+    rc = rhj_exchange_wait(ctx, which, stream);  // this rank's own stores of the relation are done
+    if (rc) return rc;
+  }
+  RHJ_CUDA(cudaEventRecord(ctx->ev_wait1[which], st));
   const int k = which;
   const bool other_done = ctx->rel_partitioned[k ^ 1];
   if (ctx->cfg.enable_two_level && ctx->nowned > 0) {
     const uint32_t L = ctx->L;
     // while the other relation is still being pushed, leave it some SMs
-    ctx->reserve_sms = (ctx->staged_exchange && !other_done) ? ctx->tune_push_sms : 0;
+    const int saved_reserve = ctx->reserve_sms;
+    if (ctx->staged_exchange && !other_done) ctx->reserve_sms = std::max(ctx->reserve_sms, ctx->tune_push_sms);
     ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
     ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
                    ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
@@ -849,11 +910,14 @@ extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
     if (rc) return rc;
     rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
                         ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
-    ctx->reserve_sms = 0;
+    ctx->reserve_sms = saved_reserve;
     if (rc) return rc;
   }
   ctx->rel_partitioned[k] = true;
+  RHJ_CUDA(cudaEventRecord(ctx->ev_rel_local[k], st));
   if (other_done) {
+    // the other relation's local pass may have run on another stream
+    RHJ_CUDA(cudaStreamWaitEvent(st, ctx->ev_rel_local[k ^ 1], 0));
     rc = record(ctx, EV_LOCAL, st);
     if (rc) return rc;
     ctx->stage = 4;
@@ -1101,6 +1165,12 @@ extern "C" int rhj_get_timings(rhj_ctx *ctx, rhj_timings *out) {
   out->lp_us = us(EV_NET, EV_LOCAL);
   out->bp_us = us(EV_LOCAL, EV_BP);
   out->h2d_us = ctx->h2d_us;
+  for (int k = 0; k < 2; ++k) {
+    if (!ctx->wait_timed[k]) continue;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ctx->ev_wait0[k], ctx->ev_wait1[k]) == cudaSuccess) out->snetcompl_us += (double)ms * 1000.0;
+    else cudaGetLastError();
+  }
   return RHJ_OK;
 }
 

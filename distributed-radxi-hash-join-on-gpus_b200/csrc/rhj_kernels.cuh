@@ -462,14 +462,12 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
 //   bin_base  [nsegs][nbins] u64: byte address of this rank's first slot of (seg, bin)
 //   chunk_off [chunk][nbins] u32: exclusive per-chunk offsets from k_colscan (tuples)
 // ---------------------------------------------------------------------------------
-constexpr uint32_t kWcListCap = 128;      // line items per warp and round
-constexpr uint32_t kWcLinesPerRound = 4;  // lines one bin contributes per round (32 * 4 = kWcListCap)
-
 template <int CFIX>
 __host__ __device__ constexpr uint32_t wc_rebase() { return CFIX == 0 ? 16384u : (CFIX % 16 == 0 ? (uint32_t)CFIX : 2u * CFIX); }
 
 __host__ __device__ inline size_t scatter_wc_smem_bytes(uint32_t nbins, uint32_t ring, uint32_t tpb) {
-  return (size_t)nbins * ring * 8 + (size_t)nbins * (8 + 4 + 2) + (size_t)(tpb / 32) * kWcListCap * 4 + 16;
+  (void)tpb;
+  return (size_t)nbins * ring * 8 + (size_t)nbins * (8 + 4 + 2) + 16;
 }
 
 __device__ __forceinline__ void st_stream_v2(void *p, const ulonglong2 &v) {
@@ -480,6 +478,12 @@ __device__ __forceinline__ uint32_t atoms_inc(uint32_t addr) {
   uint32_t old;
   asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr) : "memory");
   return old;
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)v) : "memory");
 }
 __device__ __forceinline__ void sts_u64(uint32_t addr, uint64_t v) {
   asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
@@ -492,7 +496,7 @@ __device__ __forceinline__ ulonglong2 lds_v2(uint32_t addr) {
 
 // CFIX: ring size as a compile-time constant (24 or 48 tuples), or 0 = a power of two given at run time
 template <class Source, class Map, int TPB, int IPT, int CFIX>
-__global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
+__global__ void __launch_bounds__(TPB, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1)
     k_scatter_wc(const Source src, const Map cm, const uint32_t nbins, const uint32_t ring_tuples,
                  const uint32_t *__restrict__ chunk_off, const uint64_t *__restrict__ bin_base,
                  const int *__restrict__ status, const int l2_ahead) {
@@ -505,8 +509,7 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
   uint64_t *const ring = reinterpret_cast<uint64_t *>(sh_raw);      // [nbins][C]
   uint64_t *const base = ring + (size_t)nbins * C;                  // [nbins] line-aligned byte address of position 0
   uint32_t *const word = reinterpret_cast<uint32_t *>(base + nbins);  // [nbins] (limit << 16) | next position
-  uint32_t *const list = word + nbins;                              // [NW][kWcListCap]
-  uint16_t *const head = reinterpret_cast<uint16_t *>(list + NW * kWcListCap);  // [nbins] first position still in the ring
+  uint16_t *const head = reinterpret_cast<uint16_t *>(word + nbins);  // [nbins] first position still in the ring
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t cmask = C - 1;
   // ring slot of a position that is still in the ring (q < rebase unit + ring size when CFIX != 0)
@@ -517,6 +520,7 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
     return q;
   };
   const uint32_t sa_ring = pin_u32(smem_u32(ring)), sa_word = pin_u32(smem_u32(word));
+  const uint32_t sa_head = pin_u32(smem_u32(head)), sa_base = pin_u32(smem_u32(base));
 
   const uint32_t nchunks = cm.count();
   const uint32_t c_begin = (uint32_t)((uint64_t)blockIdx.x * nchunks / gridDim.x);
@@ -532,31 +536,31 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
   // also bind bins whose destination does not continue where they stand (mode 1: their
   // remainder goes out as a partial line first); mode 2 empties everything.
   // Runs between two barriers: nobody places tuples meanwhile.
+  const uint32_t bpw = nbins >= NW ? nbins / NW : 1u;  // bins a warp owns
+  const uint32_t first = warp * bpw;
+  const uint32_t sub = lane >> 3, sub2 = 2 * (lane & 7);
   auto flush = [&](const int mode, const uint32_t c, const uint32_t seg) {
-    const uint32_t bpw = nbins >= NW ? nbins / NW : 1u;
-    const uint32_t first = warp * bpw;
-    uint32_t *const mylist = list + warp * kWcListCap;
     for (uint32_t g0 = 0; g0 < bpw; g0 += 32) {
+      // lane = bin: what leaves the ring, and the bin's state afterwards
       const uint32_t idx = g0 + lane, bin = first + idx;
       const bool valid = idx < bpw && bin < nbins;
-      uint32_t t = 0, fa = 0, fb = 0, nh = 0, nl = 0, line0 = 0;
+      uint32_t t = 0, fa = 0, fb = 0, nh = 0;
       uint64_t b = 0;
       if (valid) {
-        const uint32_t w32 = word[bin];
+        const uint32_t w32 = lds_u32(sa_word + bin * 4);
         t = w32 & 0xFFFFu;
         const uint32_t lim = w32 >> 16;
-        const uint32_t h = head[bin];
-        b = base[bin];
-        bool all = mode == 2 || t >= lim;
+        const uint32_t h = lds_u16(sa_head + bin * 2);
+        const bool all = mode == 2 || t >= lim;
         bool rebind = false;
         uint64_t new_addr = 0;
         if (mode == 1) {
+          b = lds_u64(sa_base + bin * 8);
           new_addr = bin_base[(size_t)seg * nbins + bin] + (uint64_t)chunk_off[(size_t)c * nbins + bin] * 8;
-          rebind = new_addr != b + (uint64_t)t * 8;
-          all = all || rebind;
+          rebind = new_addr != b + (uint64_t)t * 8;  // the remainder goes out first, then the bin is bound anew
         }
         fa = h;
-        if (all) {
+        if (all || rebind) {
           fb = t < lim ? t : lim;  // what the ring holds; later positions went straight to memory
           nh = t;
         } else {
@@ -564,49 +568,47 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
           fb = e > h ? e : h;
           nh = fb;
         }
-        if (fb > fa) {
-          line0 = fa & ~15u;
-          nl = (fb + 15 - line0) >> 4;
-        }
         if (rebind) {  // applied when the state is written back below
           b = new_addr & ~uint64_t(127);
           t = nh = (uint32_t)(new_addr >> 3) & 15u;
         }
       }
       const uint32_t range = fa | (fb << 16);
-      uint32_t done = 0;
-      while (__any_sync(FULL, nl > done)) {
-        const uint32_t k = nl > done ? min(nl - done, kWcLinesPerRound) : 0u;
-        const uint32_t incl = warp_inclusive_scan(k);
-        const uint32_t total = __shfl_sync(FULL, incl, 31);
-        for (uint32_t j = 0; j < k; ++j) mylist[incl - k + j] = (lane << 16) | (line0 + (done + j) * 16);
-        __syncwarp();
-        for (uint32_t i0 = 0; i0 < total; i0 += 4) {
-          const uint32_t i = i0 + (lane >> 3);
-          const uint32_t ent = i < total ? mylist[i] : 0u;
-          const uint32_t owner = ent >> 16, ql = ent & 0xFFFFu;
-          const uint32_t r = __shfl_sync(FULL, range, owner);
-          if (i < total) {
-            const uint32_t fa_i = r & 0xFFFFu, fb_i = r >> 16;
-            const uint32_t bin_i = first + g0 + owner;
-            const uint64_t b_i = base[bin_i];  // still the value the positions in the ring refer to
-            const uint32_t q0 = ql + 2 * (lane & 7);
-            const uint64_t *const rp = ring + (size_t)bin_i * C;
+      // four bins with something to copy at a time: eight lanes per bin, 16 bytes per lane and line
+      uint32_t pending = __ballot_sync(FULL, fb > fa);
+      while (pending) {
+        uint32_t m = pending;
+        uint32_t owner = __ffs(m) - 1;
+        m &= m - 1;
+        if (sub >= 1) owner = __ffs(m) - 1;
+        m &= m - 1;
+        if (sub >= 2) owner = __ffs(m) - 1;
+        m &= m - 1;
+        if (sub >= 3) owner = __ffs(m) - 1;
+        m &= m - 1;
+        pending = m;
+        const uint32_t r = __shfl_sync(FULL, range, owner & 31);
+        if (owner < 32) {
+          const uint32_t fa_i = r & 0xFFFFu, fb_i = r >> 16;
+          const uint32_t bin_i = first + g0 + owner;
+          const uint64_t b_i = lds_u64(sa_base + bin_i * 8);  // still the value the ring's positions refer to
+          const uint32_t sa_bin = sa_ring + bin_i * C * 8;
+          for (uint32_t ql = fa_i & ~15u; ql < fb_i; ql += 16) {
+            const uint32_t q0 = ql + sub2;
             if (fa_i <= ql && ql + 16 <= fb_i) {
-              const ulonglong2 v = lds_v2(sa_ring + (bin_i * C + slot(q0)) * 8);
-              st_stream_v2(reinterpret_cast<void *>(b_i + (uint64_t)q0 * 8), v);
+              st_stream_v2(reinterpret_cast<void *>(b_i + (uint64_t)q0 * 8), lds_v2(sa_bin + slot(q0) * 8));
             } else {
               if (fa_i <= q0 && q0 < fb_i)
-                st_stream_u64(reinterpret_cast<uint64_t *>(b_i + (uint64_t)q0 * 8), rp[slot(q0)]);
+                st_stream_u64(reinterpret_cast<uint64_t *>(b_i + (uint64_t)q0 * 8), lds_u64(sa_bin + slot(q0) * 8));
               if (fa_i <= q0 + 1 && q0 + 1 < fb_i)
-                st_stream_u64(reinterpret_cast<uint64_t *>(b_i + (uint64_t)(q0 + 1) * 8), rp[slot(q0 + 1)]);
+                st_stream_u64(reinterpret_cast<uint64_t *>(b_i + (uint64_t)(q0 + 1) * 8), lds_u64(sa_bin + slot(q0 + 1) * 8));
             }
           }
         }
-        __syncwarp();
-        done += k;
       }
-      if (valid) {
+      __syncwarp();
+      if (valid && (mode == 1 || nh != fa)) {
+        if (mode != 1) b = lds_u64(sa_base + bin * 8);
         if (nh >= M) {
           const uint32_t k = (nh / M) * M;
           nh -= k;
@@ -614,9 +616,9 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
           b += (uint64_t)k * 8;
         }
         const uint32_t lim = (nh & ~15u) + C;
-        word[bin] = (lim << 16) | t;
-        head[bin] = (uint16_t)nh;
-        base[bin] = b;
+        sts_u32(sa_word + bin * 4, (lim << 16) | t);
+        sts_u16(sa_head + bin * 2, nh);
+        sts_u64(sa_base + bin * 8, b);
       }
     }
   };
@@ -675,11 +677,13 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
   uint64_t pos = cb;
   Raw raw[IPT];
   load_raw(in0 + pos, (uint32_t)min((uint64_t)BATCH, ce - pos), raw);
-  if (tid == 0)
-    for (int a = 1; a <= l2_ahead; ++a) {
-      const uint64_t p = pos + (uint64_t)a * BATCH;
-      if (p < in_end) prefetch_l2_range(in0 + p, min((uint64_t)BATCH, in_end - p) * sizeof(Raw));
-    }
+  // L2 prefetch window: [pos + dist, pos + dist + BATCH) with pos = start of the batch in registers;
+  // l2_ahead is the distance in quarter batches (measured optimum: one batch; two or more thrash L2)
+  const uint64_t l2_dist = (uint64_t)l2_ahead * (BATCH / 4);
+  if (tid == 0 && l2_ahead > 0) {
+    const uint64_t p = pos + BATCH;
+    if (p < in_end) prefetch_l2_range(in0 + p, min(l2_dist, in_end - p) * sizeof(Raw));
+  }
   bool chunk_start = true;
   while (true) {
     const uint32_t n = (uint32_t)min((uint64_t)BATCH, ce - pos);
@@ -697,7 +701,7 @@ __global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
     }
     load_raw(in0 + pos, (uint32_t)min((uint64_t)BATCH, ce - pos), raw);
     if (tid == 0 && l2_ahead > 0) {
-      const uint64_t p = pos + (uint64_t)l2_ahead * BATCH;
+      const uint64_t p = pos + l2_dist;
       if (p < in_end) prefetch_l2_range(in0 + p, min((uint64_t)BATCH, in_end - p) * sizeof(Raw));
     }
   }

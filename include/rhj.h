@@ -95,6 +95,10 @@ typedef struct rhj_timings {
   double lp_us;     /* LPTASKTIME */
   double bp_us;     /* BPTASKTIME */
   double h2d_us;    /* host->device staging (rhj_join_host only), else 0 */
+  double snetcompl_us; /* SNETCOMPL (performance/Measurements.cpp:157-165, 177; operators/HashJoin.cpp:119-121):
+                          waiting for the network pass to complete on all ranks = sum over both relations of the
+                          time between rhj_exchange_wait and the start of that relation's local pass (the launcher's
+                          barrier lies in between); 0 with one rank.  Included in lp_us. */
 } rhj_timings;
 
 /* Peer-visible description of a rank's receive windows (replaces MPI_Win_create,
@@ -172,6 +176,13 @@ int rhj_get_write_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *str
  * into the owning rank's window (peer stores replace MPI_Put).  Uses the inputs
  * given to rhj_histogram.  All ranks must finish (barrier) before the next stage. */
 int rhj_network_partition(rhj_ctx *ctx, void *stream);
+/* The same, one relation at a time (which: 0 inner, 1 outer), on a stream of the caller's choice, so that
+ * a multi-rank launcher can start the inner relation's barrier + local pass while the outer relation is
+ * still crossing NVLink. */
+int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream);
+/* Number of SMs the kernels launched after this call may occupy (0 = all).  For launchers that run
+ * two stages side by side on two streams (an NVLink-bound network pass next to an HBM-bound local pass). */
+int rhj_set_sm_limit(rhj_ctx *ctx, int sms);
 
 /* TASK_PARTITION -- tasks/LocalPartitioning.cpp:59-250 for every owned partition:
  * histogram, 8-tuple padded prefix, scatter.  No-op unless enable_two_level. */
