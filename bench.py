@@ -281,7 +281,7 @@ def run_ours(args):
 
     n = 1 << args.log2n          # tuples per relation per GPU
     G = n * world                # global relation size
-    flags = (rhj.FLAG_HIST_WARP_AGGREGATE if args.agg else 0) | (rhj.FLAG_STAGE_HOST_INPUTS if world == 1 else 0)
+    flags = (rhj.FLAG_HIST_WARP_AGGREGATE if args.agg else 0) | (0 if args.no_e2e else rhj.FLAG_STAGE_HOST_INPUTS)
     flags |= rhj.FLAG_DEBUG_ENV if args.debug_env else 0
     # radix bits: sub-partitions of ~4096 build tuples (one shared-memory table) need
     # log2(global size / 4096) bits in total; weak scaling adds log2(N) bits
@@ -316,47 +316,14 @@ def run_ours(args):
         else:
             rhj.join_multi_rank(ctx, inner, outer)
 
-    m64 = (1 << 64) - 1
-
-    def expected_checksum():
-        """(count, sum key, sum rid_R, sum rid_S, sum mix) of the whole job, computed on the device
-        independently of the join: pos[key_R] = rid_R for every inner tuple of every rank, gathered at
-        this rank's outer keys, then the mix term (rhj_device.cuh mix_triple == oracle orc_mix) in
-        wrap-around int64 arithmetic.  All five words are all-reduced over the ranks."""
-        pos = torch.empty(G, dtype=torch.int64, device=dev)
-        for r in range(world):
-            blk = d_inner.clone() if r == rank else torch.empty_like(d_inner)
-            if world > 1:
-                dist.broadcast(blk, src=r)
-            v = blk.view(-1, 2)
-            pos[v[:, 0]] = v[:, 1]
-            del blk, v
-        so = d_outer.view(-1, 2)
-        tot = torch.zeros(5, dtype=torch.int64, device=dev)
-        stepn = 1 << 24
-        lo32 = 0xFFFFFFFF
-        for b in range(0, n, stepn):
-            key, rs = so[b:b + stepn, 0], so[b:b + stepn, 1]
-            rr = pos[key]
-            k32 = (key ^ (key >> 32)) & lo32
-            r32 = (rr ^ (rr >> 32)) & lo32
-            s32 = (rs ^ (rs >> 32)) & lo32
-            mix = (r32 ^ 0x9E3779B9) * (s32 ^ 0x85EBCA6B) + (k32 ^ 0xC2B2AE35) * ((r32 + s32 + 0x27D4EB2F) & lo32)
-            tot += torch.stack([torch.tensor(key.numel(), device=dev), key.sum(), rr.sum(), rs.sum(), mix.sum()])
-        del pos
-        if world > 1:
-            dist.all_reduce(tot)  # int64 wrap-around sum == arithmetic modulo 2^64
-        return [int(x) & m64 for x in tot.tolist()]
-
-    want = expected_checksum()
+    from tools import checksum as CK
+    m64 = CK.M64
+    want = CK.expected_result(torch, dist, d_inner, n, d_outer, n, G, world, rank, dev)
     closed = (G * (G - 1) // 2) & m64
     assert want[0] == G and want[1] == closed and want[2] == closed and want[3] == closed, want
 
     def check(res):
-        tot = torch.tensor([x - (1 << 64) if x >= (1 << 63) else x for x in res.astuple()], dtype=torch.int64, device=dev)
-        if world > 1:
-            dist.all_reduce(tot)
-        got = [int(x) & m64 for x in tot.tolist()]
+        got = CK.reduce_result(torch, dist, res, world, dev)
         assert got == want, f"result {got} != expected {want} (count, sum key, sum rid_R, sum rid_S, sum mix)"
 
     # untimed prologue: the reference's own workload (main.cpp:94-104 generator + distribute) at
@@ -405,12 +372,14 @@ def run_ours(args):
     net_launch_us = stage_us["jmpi_us"] / 2.0
     net_bytes = BYTES_PER_TUPLE["net"] * n
     achieved = net_bytes / (net_launch_us * 1e-6) / 1e9 if net_launch_us > 0 else 0.0
+    # DRAM bytes per launch from an ncu capture of exactly this configuration, else null
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_scatter_network_bytes_per_launch")
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic_r02.json")))
+        traffic = tr.get(f"n{world}_bits{net_bits}+{loc_bits}_log2n{args.log2n}", {}).get("k_scatter_wc_network_bytes_per_launch")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "k_scatter3<InputSource<16>> (network partitioning pass)",
+    roofline = {"bound": "hbm", "kernel": "k_scatter_wc<InputSource<16>> (network partitioning pass)",
                 "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": net_bytes, "launch_us": net_launch_us}
@@ -422,31 +391,32 @@ def run_ours(args):
         stages[key] = {"us": us, "GBps": gbs, "frac_of_hbm_peak": gbs / hbm_peak}
     whole = BYTES_PER_TUPLE["total"] * 2 * n / (step_us * 1e-6) / 1e9
     stages["join"] = {"us": step_us, "GBps": whole, "frac_of_hbm_peak": whole / hbm_peak}
+    # SNETCOMPL: waiting for the other ranks' stores (barrier), part of `local` in the reference's keys too
+    stages["exchange_wait"] = {"us": tm["snetcompl_us"]}
+    roofline_nvlink = None
+    if world > 1:
+        # the exchange is fused into the network pass: every tuple bound for another rank crosses
+        # NVLink as part of a full 128-byte line stored by k_scatter_wc
+        nv_bytes = 2 * 8 * n * (world - 1) / world  # both relations, per GPU and direction
+        nv_gbs = nv_bytes / (stage_us["jmpi_us"] * 1e-6) / 1e9 if stage_us["jmpi_us"] > 0 else 0.0
+        roofline_nvlink = {"bound": "nvlink", "bytes_per_gpu_per_direction": nv_bytes, "us": stage_us["jmpi_us"],
+                           "achieved": nv_gbs, "peak": 900.0, "unit": "GB/s", "frac": nv_gbs / 900.0,
+                           "frac_of_measured_peer_copy_770": nv_gbs / 770.0,
+                           "how": "8 B x tuples x (N-1)/N per relation / device time of the network pass (cudaEvents)"}
 
     # ---- end to end: host buffers in, result out -------------------------------------------
     e2e = None
     if not args.no_e2e:
         nbytes = n * 16
-        if world == 1:
-            pin_i, pin_o = rhj.PinnedBuffer(nbytes), rhj.PinnedBuffer(nbytes)
-            rhj.check(L.rhj_memcpy_d2h(pin_i.ptr, d_inner.data_ptr(), nbytes))
-            rhj.check(L.rhj_memcpy_d2h(pin_o.ptr, d_outer.data_ptr(), nbytes))
+        pin_i, pin_o = rhj.PinnedBuffer(nbytes), rhj.PinnedBuffer(nbytes)
+        rhj.check(L.rhj_memcpy_d2h(pin_i.ptr, d_inner.data_ptr(), nbytes))
+        rhj.check(L.rhj_memcpy_d2h(pin_o.ptr, d_outer.data_ptr(), nbytes))
 
-            def e2e_step():
+        def e2e_step():
+            if world == 1:
                 return ctx.join_host(pin_i.ptr, n, pin_o.ptr, n)
-        else:
-            h_i = torch.empty(2 * n, dtype=torch.int64).pin_memory()
-            h_o = torch.empty(2 * n, dtype=torch.int64).pin_memory()
-            h_i.copy_(d_inner)
-            h_o.copy_(d_outer)
-            s_i, s_o = torch.empty_like(d_inner), torch.empty_like(d_outer)
-            rel_i, rel_o = rhj.Relation(s_i, n, G), rhj.Relation(s_o, n, G)
-
-            def e2e_step():
-                s_i.copy_(h_i, non_blocking=True)
-                s_o.copy_(h_o, non_blocking=True)
-                rhj.join_multi_rank(ctx, rel_i, rel_o)
-                return ctx.result()
+            rhj.join_multi_rank(ctx, inner, outer, host=(pin_i.ptr, pin_o.ptr))
+            return ctx.result()
         r = e2e_step()  # warm-up
         barrier()
         t0 = time.perf_counter()
@@ -461,7 +431,7 @@ def run_ours(args):
                "h2d_bytes_per_step": 2 * nbytes * world, "d2h_bytes_per_step": 40 * world,
                "steps": args.e2e_steps, "ms_per_step": float(dt.item()) * 1e3 / args.e2e_steps,
                "api": "rhj_join_host (pinned host buffers)" if world == 1 else
-                      "HashJoin launcher: pinned host -> device copy + staged join per rank"}
+                      "rhj_stage_host_inputs (pinned host buffers) + the stage entry points, one process per GPU"}
     clocks = sampler.stop() if rank == 0 else None
 
     cpu = None
@@ -477,8 +447,9 @@ def run_ours(args):
                            "radix_bits": f"{net_bits} network + {loc_bits} local", "tuple_bytes": 16,
                            "l2": "inputs (8 GiB per GPU) are larger than L2; no flush needed",
                            "exchange": "none (1 GPU)" if world == 1 else
-                           "local send buffers pushed with coalesced P2P stores over NVLink (CUDA IPC windows)"},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+                           "fused: the scatter kernel stores full 128-byte lines into the owners' windows over NVLink "
+                           "(CUDA IPC); outer network pass beside the inner local pass from 4 GPUs on"},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "roofline_nvlink": roofline_nvlink,
                 "stages": stages, "cpu_baseline": cpu,
                 "result": {"matches": G, "checksum_ok": True, "checksum_words": 5}, "parity": parity}
         print(json.dumps(line), flush=True)

@@ -117,7 +117,9 @@ SYMBOLS = {
     "rhj_get_timings": (_int, [_vp, C.POINTER(Timings)]),
     "rhj_join": (_int, [_vp, _vp, _u64, _vp, _u64, _vp, _resp]),
     "rhj_join_host": (_int, [_vp, _vp, _u64, _vp, _u64, _vp, _resp]),
+    "rhj_stage_host_inputs": (_int, [_vp, _vp, _u64, _vp, _u64, _vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "rhj_fill_perm": (_int, [_vp, _u32, _u64, _u64, _u64, _u64, _u64, _u64, _u64, _vp]),
+    "rhj_apply_perm": (_int, [_vp, _u64, _u32, _u64, _u64, _vp]),
     "rhj_local_histogram_noalloc": (_int, [_vp, _u32, _u64, _u32, _vp, _vp]),
     "rhj_host_alloc": (_int, [C.POINTER(_vp), _u64]),
     "rhj_host_free": (_int, [_vp]),
@@ -200,6 +202,10 @@ class Context:
         h = _vp()
         check(lib().rhj_init(C.byref(h), rank, nranks, device, C.byref(cfg)))
         self.h = h
+
+    def sm_count(self) -> int:
+        import torch
+        return torch.cuda.get_device_properties(self.device).multi_processor_count
 
     def close(self):
         if getattr(self, "h", None):
@@ -346,6 +352,14 @@ class Context:
         """All stages enqueued, no host synchronisation (result via .result())."""
         check(lib().rhj_join(self.h, _ptr(inner), inner_n, _ptr(outer), outer_n, _stream(), None))
 
+    def stage_host_inputs(self, inner_host, inner_n: int, outer_host, outer_n: int):
+        """Host relations -> the context's device staging buffers (asynchronous on the current stream);
+        returns the two device addresses to hand to histogram()."""
+        a, b = _vp(), _vp()
+        check(lib().rhj_stage_host_inputs(self.h, _ptr(inner_host), inner_n, _ptr(outer_host), outer_n, _stream(),
+                                          C.byref(a), C.byref(b)))
+        return a.value or 0, b.value or 0
+
     def join_host(self, inner_host, inner_n: int, outer_host, outer_n: int) -> Result:
         r = Result()
         check(lib().rhj_join_host(self.h, _ptr(inner_host), inner_n, _ptr(outer_host), outer_n, _stream(), C.byref(r)))
@@ -373,6 +387,11 @@ def fill_perm(tensor, tuple_bytes: int, n: int, first: int, domain: int, seed: i
               start_key: int = 0, start_rid: int = 0):
     """Device generator, bit-identical to oracle.orc_fill_perm (harness-owned; Relation.cpp:63-85 stand-in)."""
     check(lib().rhj_fill_perm(_ptr(tensor), tuple_bytes, n, first, domain, seed, modulo, start_key, start_rid, _stream()))
+
+
+def apply_perm(tensor, n: int, stride_words: int, domain: int, seed: int):
+    """tensor[i * stride_words] <- perm(tensor[i * stride_words]) with fill_perm's bijection of (domain, seed)."""
+    check(lib().rhj_apply_perm(_ptr(tensor), n, stride_words, domain, seed, _stream()))
 
 
 from .hashjoin import HashJoin, Relation, join_multi_rank  # noqa: E402,F401

@@ -122,7 +122,7 @@ struct rhj_ctx {
   bool local_planned = false;
   cudaEvent_t ev[EV_COUNT] = {};
   bool ev_valid[EV_COUNT] = {};
-  double h2d_us = 0;
+  bool staged_pending = false;  // rhj_stage_host_inputs ran since the last rhj_histogram
 
   // kernel choice and ablation knobs (rhj_init; environment only with RHJ_FLAG_DEBUG_ENV)
   int tune_scatter = 3;  // 0 first generation, 2 offset-driven tiles, 3 write-combining rings (default)
@@ -692,6 +692,8 @@ extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner
   ctx->input_n[1] = outer_n;
   for (int k = 0; k < 2; ++k) ctx->nchunks1[k] = (uint32_t)((ctx->input_n[k] + ctx->chunk1 - 1) / ctx->chunk1);
   ctx->local_planned = false;
+  ctx->ev_valid[EV_H2D0] = ctx->staged_pending;  // h2d_us only when this join's inputs were staged
+  ctx->staged_pending = false;
   for (int k = 0; k < 2; ++k) ctx->rel_partitioned[k] = ctx->rel_scattered[k] = ctx->wait_timed[k] = false;
   int rc = record(ctx, EV_START, st);
   if (rc) return rc;
@@ -890,6 +892,8 @@ extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
   }
   RHJ_CUDA(cudaEventRecord(ctx->ev_wait1[which], st));
   const int k = which;
+  // the other relation's local pass may have run on another stream; its counts are read below
+  if (ctx->rel_partitioned[k ^ 1]) RHJ_CUDA(cudaStreamWaitEvent(st, ctx->ev_rel_local[k ^ 1], 0));
   const bool other_done = ctx->rel_partitioned[k ^ 1];
   if (ctx->cfg.enable_two_level && ctx->nowned > 0) {
     const uint32_t L = ctx->L;
@@ -916,8 +920,6 @@ extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
   ctx->rel_partitioned[k] = true;
   RHJ_CUDA(cudaEventRecord(ctx->ev_rel_local[k], st));
   if (other_done) {
-    // the other relation's local pass may have run on another stream
-    RHJ_CUDA(cudaStreamWaitEvent(st, ctx->ev_rel_local[k ^ 1], 0));
     rc = record(ctx, EV_LOCAL, st);
     if (rc) return rc;
     ctx->stage = 4;
@@ -1164,7 +1166,7 @@ extern "C" int rhj_get_timings(rhj_ctx *ctx, rhj_timings *out) {
   out->jproc_us = us(EV_NET, EV_BP);
   out->lp_us = us(EV_NET, EV_LOCAL);
   out->bp_us = us(EV_LOCAL, EV_BP);
-  out->h2d_us = ctx->h2d_us;
+  out->h2d_us = ctx->ev_valid[EV_H2D0] ? us(EV_H2D0, EV_START) : 0.0;
   for (int k = 0; k < 2; ++k) {
     if (!ctx->wait_timed[k]) continue;
     float ms = 0;
@@ -1187,7 +1189,6 @@ extern "C" int rhj_join(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, c
     int rc = rhj_plan(ctx, inner_n, outer_n, 0, 0);
     if (rc) return rc;
   }
-  ctx->h2d_us = 0;
   int rc = rhj_histogram(ctx, inner_dev, inner_n, outer_dev, outer_n, stream);
   if (!rc) rc = rhj_compute_offsets(ctx, nullptr, stream);
   if (!rc) rc = rhj_network_partition(ctx, stream);
@@ -1197,38 +1198,49 @@ extern "C" int rhj_join(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, c
   return rc;
 }
 
+// Host relations -> the staging buffers rhj_plan reserved (RHJ_FLAG_STAGE_HOST_INPUTS), for any number of
+// ranks: the multi-rank form of what rhj_join_host does before it joins.
+extern "C" int rhj_stage_host_inputs(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host,
+                                     uint64_t outer_n, void *stream, void **inner_dev, void **outer_dev) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (!(ctx->cfg.flags & RHJ_FLAG_STAGE_HOST_INPUTS))
+    return fail(RHJ_ERR_STATE, "rhj_stage_host_inputs needs RHJ_FLAG_STAGE_HOST_INPUTS in rhj_config.flags (device staging buffers)");
+  if (!ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
+  if (inner_n > ctx->max_local[0] || outer_n > ctx->max_local[1])
+    return fail(RHJ_ERR_INVALID, "relation sizes exceed the planned maxima");
+  if ((inner_n && !inner_host) || (outer_n && !outer_host)) return fail(RHJ_ERR_INVALID, "NULL relation pointer");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RHJ_CUDA(cudaEventRecord(ctx->ev[EV_H2D0], st));
+  ctx->staged_pending = true;
+  RHJ_CUDA(cudaMemcpyAsync(ctx->staged_input[0], inner_host, inner_n * ctx->cfg.tuple_bytes, cudaMemcpyHostToDevice, st));
+  RHJ_CUDA(cudaMemcpyAsync(ctx->staged_input[1], outer_host, outer_n * ctx->cfg.tuple_bytes, cudaMemcpyHostToDevice, st));
+  if (inner_dev) *inner_dev = ctx->staged_input[0];
+  if (outer_dev) *outer_dev = ctx->staged_input[1];
+  return RHJ_OK;
+}
+
 extern "C" int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host,
                              uint64_t outer_n, void *stream, rhj_result *out) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (!(ctx->cfg.flags & RHJ_FLAG_STAGE_HOST_INPUTS))
     return fail(RHJ_ERR_STATE, "rhj_join_host needs RHJ_FLAG_STAGE_HOST_INPUTS in rhj_config.flags (device staging buffers)");
+  if (ctx->nranks != 1)
+    return fail(RHJ_ERR_STATE, "rhj_join_host drives a single rank; with %d ranks call rhj_stage_host_inputs and the stages", ctx->nranks);
   if (!ctx->planned) {
     int rc = rhj_plan(ctx, inner_n, outer_n, 0, 0);
     if (rc) return rc;
   }
-  if (inner_n > ctx->max_local[0] || outer_n > ctx->max_local[1])
-    return fail(RHJ_ERR_INVALID, "relation sizes exceed the planned maxima");
-  RHJ_CUDA(cudaSetDevice(ctx->device));
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  RHJ_CUDA(cudaEventRecord(ctx->ev[EV_H2D0], st));
-  RHJ_CUDA(cudaMemcpyAsync(ctx->staged_input[0], inner_host, inner_n * ctx->cfg.tuple_bytes, cudaMemcpyHostToDevice, st));
-  RHJ_CUDA(cudaMemcpyAsync(ctx->staged_input[1], outer_host, outer_n * ctx->cfg.tuple_bytes, cudaMemcpyHostToDevice, st));
-  int rc = rhj_join(ctx, ctx->staged_input[0], inner_n, ctx->staged_input[1], outer_n, stream, out);
+  void *di = nullptr, *dout = nullptr;
+  int rc = rhj_stage_host_inputs(ctx, inner_host, inner_n, outer_host, outer_n, stream, &di, &dout);
   if (rc) return rc;
-  float ms = 0;
-  if (cudaEventElapsedTime(&ms, ctx->ev[EV_H2D0], ctx->ev[EV_START]) == cudaSuccess) ctx->h2d_us = ms * 1000.0;
-  else cudaGetLastError();
-  return RHJ_OK;
+  return rhj_join(ctx, di, inner_n, dout, outer_n, stream, out);
 }
 
 // -----------------------------------------------------------------------------------
 // device generator
 // -----------------------------------------------------------------------------------
-extern "C" int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n, uint64_t first, uint64_t domain,
-                             uint64_t seed, uint64_t modulo, uint64_t start_key, uint64_t start_rid, void *stream) {
-  if (tuple_bytes != 16 && tuple_bytes != 8) return fail(RHJ_ERR_INVALID, "tuple_bytes must be 16 or 8");
-  if (n == 0) return RHJ_OK;
-  if (!tuples_dev) return fail(RHJ_ERR_INVALID, "NULL tuples");
+static PermParams make_perm(uint64_t domain, uint64_t seed) {
   PermParams pp{};
   pp.domain = domain;
   uint32_t b = 0;
@@ -1238,6 +1250,25 @@ extern "C" int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n,
   pp.m0 = splitmix64(seed) | 1; pp.a0 = splitmix64(seed + 1);
   pp.m1 = splitmix64(seed + 2) | 1; pp.a1 = splitmix64(seed + 3);
   pp.m2 = splitmix64(seed + 4) | 1; pp.a2 = splitmix64(seed + 5);
+  return pp;
+}
+
+extern "C" int rhj_apply_perm(uint64_t *vals_dev, uint64_t n, uint32_t stride_words, uint64_t domain, uint64_t seed,
+                              void *stream) {
+  if (n == 0) return RHJ_OK;
+  if (!vals_dev || stride_words == 0) return fail(RHJ_ERR_INVALID, "NULL values or zero stride");
+  uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, 148 * 16);
+  k_apply_perm<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(vals_dev, n, stride_words, make_perm(domain, seed));
+  RHJ_CHECK_LAUNCH("k_apply_perm");
+  return RHJ_OK;
+}
+
+extern "C" int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n, uint64_t first, uint64_t domain,
+                             uint64_t seed, uint64_t modulo, uint64_t start_key, uint64_t start_rid, void *stream) {
+  if (tuple_bytes != 16 && tuple_bytes != 8) return fail(RHJ_ERR_INVALID, "tuple_bytes must be 16 or 8");
+  if (n == 0) return RHJ_OK;
+  if (!tuples_dev) return fail(RHJ_ERR_INVALID, "NULL tuples");
+  const PermParams pp = make_perm(domain, seed);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, 148 * 16);
   if (tuple_bytes == 16) k_fill_perm<16><<<grid, 256, 0, st>>>(tuples_dev, n, first, pp, modulo, start_key, start_rid);

@@ -514,10 +514,13 @@ __global__ void __launch_bounds__(TPB, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1)
   const uint32_t cmask = C - 1;
   // ring slot of a position that is still in the ring (q < rebase unit + ring size when CFIX != 0)
   auto slot = [&](uint32_t q) -> uint32_t {
-    if (CFIX == 0) return q & cmask;
-    if (q >= (uint32_t)CFIX) q -= CFIX;
-    if (M > (uint32_t)CFIX && q >= (uint32_t)CFIX) q -= CFIX;
-    return q;
+    if constexpr (CFIX == 0) {
+      return q & cmask;
+    } else {
+      if (q >= (uint32_t)CFIX) q -= CFIX;
+      if (M > (uint32_t)CFIX && q >= (uint32_t)CFIX) q -= CFIX;
+      return q;
+    }
   };
   const uint32_t sa_ring = pin_u32(smem_u32(ring)), sa_word = pin_u32(smem_u32(word));
   const uint32_t sa_head = pin_u32(smem_u32(head)), sa_base = pin_u32(smem_u32(base));
@@ -1792,6 +1795,13 @@ __global__ void k_fill_perm(void *tuples, uint64_t n, uint64_t first, PermParams
       reinterpret_cast<uint64_t *>(tuples)[i] = (key << 32) | (rid & 0xFFFFFFFFull);
     }
   }
+}
+
+// vals[i * stride] <- perm(vals[i * stride]): the generator's bijection applied to values that are
+// already there (rank -> key for a skewed probe side, oracle orc_fill_zipf)
+__global__ void k_apply_perm(uint64_t *vals, uint64_t n, uint32_t stride, PermParams pp) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    vals[i * stride] = perm_apply(vals[i * stride], pp);
 }
 
 }  // namespace rhj

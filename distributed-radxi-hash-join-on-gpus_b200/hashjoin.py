@@ -63,6 +63,48 @@ def exchange_windows(ctx, group=None):
             ctx.window_import(r, WindowHandle.from_buffer_copy(raw))
 
 
+def exact_window_caps(cfg, nranks: int, rank: int, inner: Relation, outer: Relation, group=None):
+    """Receive-window sizes as the reference computes them: after a histogram of the actual relations
+    (data/Window.cpp:160-178 sizes every window from assignment + global histogram, so it can never
+    overflow, however skewed the keys are).  One extra counting pass over the keys at set-up time,
+    done with torch (launcher plumbing, outside every timed join); returns one pair of capacities
+    that fits every rank, since all ranks must plan the same capacities."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from . import lib, FLAG_BALANCED_ASSIGNMENT
+    P = 1 << cfg.network_fanout_bits
+    hists = []
+    for rel in (inner, outer):
+        n = rel.local_size
+        h = torch.zeros(P, dtype=torch.int64, device=rel.data.device)
+        step = 1 << 24
+        for b in range(0, n, step):
+            e = min(n, b + step)
+            keys = rel.data[2 * b:2 * e:2] if rel.tuple_bytes == 16 else (rel.data[b:e] >> 32)
+            h += torch.bincount(keys & (P - 1), minlength=P)
+        g = [torch.zeros_like(h) for _ in range(nranks)]
+        if nranks > 1:
+            dist.all_gather(g, h, group=group)
+        else:
+            g = [h]
+        hists.append(np.ascontiguousarray(torch.stack(g).cpu().numpy().astype(np.uint64)))
+    assign = np.zeros(P, np.uint32)
+    if cfg.flags & FLAG_BALANCED_ASSIGNMENT:
+        gi = np.ascontiguousarray(hists[0].sum(axis=0, dtype=np.uint64))
+        go = np.ascontiguousarray(hists[1].sum(axis=0, dtype=np.uint64))
+        lib().rhj_host_assignment_balanced(gi.ctypes.data, go.ctypes.data, nranks, P, assign.ctypes.data)
+    else:
+        lib().rhj_host_assignment(nranks, P, assign.ctypes.data)
+    caps = []
+    for k in range(2):
+        ws = np.zeros(nranks, np.uint64)
+        lib().rhj_host_offsets_assigned(hists[k].ctypes.data, assign.ctypes.data, nranks, rank, P, None, None, None, None,
+                                        ws.ctypes.data)
+        caps.append(int(ws.max()) + 64)
+    return tuple(caps)
+
+
 _HOST_GROUPS = {}
 
 
@@ -84,39 +126,84 @@ def _host_barrier_group(group=None):
     return _HOST_GROUPS[key]
 
 
-def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=None, capacity=None):
+_SIDE_STREAMS = {}
+
+
+def _side_stream(ctx):
+    import torch
+    key = id(ctx)
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream(device=ctx.device)
+    return _SIDE_STREAMS[key]
+
+
+def overlap_sms(nranks: int, sm_count: int = 148) -> int:
+    """SMs given to the outer relation's network pass while the inner relation's local pass runs
+    beside it (0 = no overlap).  With two ranks half of the tuples stay at home and the pass is
+    HBM-bound like the local pass, so running them side by side gains nothing; from four ranks on
+    the pass waits for NVLink and half of the SMs are enough to keep the links busy."""
+    return 0 if nranks < 4 else sm_count // 2
+
+
+def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=None, capacity=None, host=None,
+                    overlap=None):
     """operators/HashJoin.cpp:45-220 for this rank; every rank calls it (collective).  With `pairs`
     (device int64 tensor, 2 values per pair) the build/probe stage also writes this rank's
-    (rid_R, rid_S) pairs (rhj_build_probe_pairs)."""
+    (rid_R, rid_S) pairs (rhj_build_probe_pairs).  `host` = (inner_host, outer_host): the relations
+    are taken from host memory through rhj_stage_host_inputs instead of `inner.data`/`outer.data`.
+    `overlap`: SMs of the outer relation's network pass (None = overlap_sms(nranks))."""
     import torch
     import torch.distributed as dist
-    ctx.histogram(inner.data, inner.local_size, outer.data, outer.local_size)
-    if ctx.nranks > 1:
-        local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr(), 2 * ctx.P), device=f"cuda:{ctx.device}")
-        gathered = torch.empty(ctx.nranks * 2 * ctx.P, dtype=torch.int64, device=local.device)
+    if host is not None:
+        d_in, d_out = ctx.stage_host_inputs(host[0], inner.local_size, host[1], outer.local_size)
+    else:
+        d_in, d_out = inner.data, outer.data
+    ctx.histogram(d_in, inner.local_size, d_out, outer.local_size)
+    if ctx.nranks == 1:
+        ctx.compute_offsets(None)
+        ctx.network_partition()
+        ctx.local_partition()
+    else:
+        dev = f"cuda:{ctx.device}"
+        local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr(), 2 * ctx.P), device=dev)
+        gathered = torch.empty(ctx.nranks * 2 * ctx.P, dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(gathered, local, group=group)
         ctx.compute_offsets(gathered)
-    else:
-        ctx.compute_offsets(None)
-    ctx.network_partition()
-    if ctx.nranks > 1:
-        # Per relation: my pushes are complete (exchange_wait), then everybody's are (the
-        # all-reduce is the barrier of operators/HashJoin.cpp:119-121).  The inner relation's
-        # local pass then runs while the outer relation is still crossing NVLink.
+        # Per relation: my stores into the peers' windows are complete (exchange_wait), then
+        # everybody's are (the all-reduce is the barrier of operators/HashJoin.cpp:119-121).
         host_group = _host_barrier_group(group)
-        token = torch.zeros(1, dtype=torch.int32, device=f"cuda:{ctx.device}")
-        for which in (0, 1):
-            if host_group is not None:
-                # optional host-side barrier (RHJ_HOST_BARRIER): host waits for its own pushes,
-                # then meets the other ranks over gloo instead of NCCL
+        token = torch.zeros(1, dtype=torch.int32, device=dev)
+
+        def barrier(which):
+            if host_group is not None:  # optional host-side barrier (RHJ_HOST_BARRIER)
                 ctx.exchange_sync(which)
                 dist.barrier(group=host_group)
             else:
                 ctx.exchange_wait(which)
                 dist.all_reduce(token, group=group)
-            ctx.local_partition_rel(which)
-    else:
-        ctx.local_partition()
+
+        sms = overlap_sms(ctx.nranks) if overlap is None else overlap
+        if sms <= 0 or host_group is not None:
+            ctx.network_partition()
+            for which in (0, 1):
+                barrier(which)
+                ctx.local_partition_rel(which)
+        else:
+            # The inner relation's barrier and local pass run on a second stream beside the outer
+            # relation's network pass, each on its share of the SMs.
+            main, side = torch.cuda.current_stream(), _side_stream(ctx)
+            ctx.network_partition_rel(0)
+            side.wait_stream(main)
+            ctx.set_sm_limit(sms)
+            ctx.network_partition_rel(1)
+            with torch.cuda.stream(side):
+                barrier(0)
+                ctx.set_sm_limit(ctx.sm_count() - sms)
+                ctx.local_partition_rel(0)
+            ctx.set_sm_limit(0)
+            barrier(1)
+            main.wait_stream(side)
+            ctx.local_partition_rel(1)
     if pairs is not None:
         ctx.build_probe_pairs(pairs, capacity)
     else:
@@ -132,7 +219,7 @@ class HashJoin:
     RESULT_CHECKSUM = (0, 0, 0, 0)
 
     def __init__(self, numberOfNodes: int, nodeId: int, innerRelation: Relation, outerRelation: Relation,
-                 config=None, device: int | None = None, group=None, window_caps=(0, 0)):
+                 config=None, device: int | None = None, group=None, window_caps=None):
         from . import Context, make_config
         import torch
         self.numberOfNodes, self.nodeId = numberOfNodes, nodeId
@@ -141,6 +228,11 @@ class HashJoin:
         cfg = config if config is not None else make_config(tuple_bytes=innerRelation.tuple_bytes)
         dev = device if device is not None else torch.cuda.current_device()
         self.ctx = Context(cfg, nodeId, numberOfNodes, dev)
+        if window_caps is None:
+            # the reference sizes each window exactly, after the histogram phase; a static guess
+            # (allocation_factor x local size) only holds for near-uniform partition sizes
+            window_caps = (0, 0) if numberOfNodes == 1 else \
+                exact_window_caps(cfg, numberOfNodes, nodeId, innerRelation, outerRelation, group)
         self.ctx.plan(innerRelation.local_size, outerRelation.local_size, *window_caps)
         exchange_windows(self.ctx, group)
 

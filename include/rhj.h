@@ -136,8 +136,15 @@ uint64_t rhj_workspace_bytes(const rhj_config *cfg, int nranks, uint64_t max_loc
 
 /* Carve windows and all intermediates out of the pool (allocating a pool of
  * exactly the right size when none exists).  Nothing is allocated afterwards.
- * window_*_cap = tuples this rank can receive per relation; 0 = allocation_factor * max_local_*.
- * Replaces Window's constructor sizing (data/Window.cpp:16-50). */
+ * window_*_cap = tuples this rank can receive per relation; 0 = allocation_factor * max_local_* + 1024.
+ * Replaces Window's constructor sizing (data/Window.cpp:16-50).  The reference sizes each window
+ * exactly, after the histogram phase (data/Window.cpp:160-178), and therefore never overflows; here
+ * the capacity is fixed before the data is seen.  The default only holds for near-uniform partition
+ * sizes: with more than one rank and skewed keys (a hot partition, a Zipf probe side) pass the exact
+ * size -- rhj_host_offsets' window_sizes from a histogram of the relations, as the HashJoin launchers
+ * do -- or a safe bound such as the global relation size.  A window that is too small is detected on
+ * the device by rhj_compute_offsets, all later kernels of the join do nothing, and rhj_get_result (the
+ * first call that synchronises) returns RHJ_ERR_CAPACITY. */
 int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_local_outer, uint64_t window_inner_cap,
              uint64_t window_outer_cap);
 
@@ -236,10 +243,23 @@ int rhj_join(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *
 int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host, uint64_t outer_n,
                   void *stream, rhj_result *out);
 
+/* The staging half of rhj_join_host for any number of ranks: copies this rank's host relations
+ * (pinned or pageable) into the device staging buffers rhj_plan reserved (RHJ_FLAG_STAGE_HOST_INPUTS)
+ * on `stream` and returns their device addresses, which the caller then hands to rhj_histogram.
+ * Replaces the per-partition PCIe upload of the reference's GPU seam (tasks/gpu/GPUWrapper.cu:38-64 ->
+ * operators/gpu/eth.cu:180-193) for multi-rank launchers; rhj_timings.h2d_us covers the copies. */
+int rhj_stage_host_inputs(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host,
+                          uint64_t outer_n, void *stream, void **inner_dev, void **outer_dev);
+
 /* ---- relation generators on the device (data/Relation.cpp:63-85 stand-ins for sizes
  * where host rand() Fisher-Yates is impractical; identical to oracle/orc_fill_perm) ---- */
 int rhj_fill_perm(void *tuples_dev, uint32_t tuple_bytes, uint64_t n, uint64_t first, uint64_t domain,
                   uint64_t seed, uint64_t modulo, uint64_t start_key, uint64_t start_rid, void *stream);
+
+/* The same bijection applied in place to values that are already on the device:
+ * vals[i * stride_words] <- perm(vals[i * stride_words]), values in [0, domain).  Maps the ranks of a
+ * skewed distribution to keys as oracle/orc_fill_zipf does. */
+int rhj_apply_perm(uint64_t *vals_dev, uint64_t n, uint32_t stride_words, uint64_t domain, uint64_t seed, void *stream);
 
 /* ---- local histogram without any allocation ----------------------------------------
  * No counterpart in the reference (its GPU seam mallocs and frees on every call,

@@ -44,13 +44,23 @@ def _worker(rank, world, port, per, knobs, out_dir):
     cfg = rhj.make_config(knobs[0], knobs[1], knobs[2], bool(knobs[3]))
     ri = rhj.Relation.from_numpy(inner[rank], per * world, device=rank)
     ro = rhj.Relation.from_numpy(outer[rank], per * world, device=rank)
-    hj = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=rank, window_caps=(per * world, per * world))
+    cfg.flags |= rhj.FLAG_STAGE_HOST_INPUTS
+    hj = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=rank)  # windows sized from a histogram, as the reference does
+    # host buffers through the C ABI (rhj_stage_host_inputs): the multi-rank form of rhj_join_host
+    rhj.join_multi_rank(hj.ctx, ri, ro, host=(np.ascontiguousarray(inner[rank]), np.ascontiguousarray(outer[rank])))
+    host_res = hj.ctx.result().astuple()
+    assert hj.ctx.timings().h2d_us > 0
     res = [hj.join().astuple() for _ in range(2)]  # twice: windows are reused
+    # the same join with the outer network pass beside the inner local pass (two streams, split SMs)
+    rhj.join_multi_rank(hj.ctx, ri, ro, overlap=hj.ctx.sm_count() // 2)
+    assert hj.ctx.result().astuple() == res[0]
+    assert hj.ctx.timings().snetcompl_us > 0
     # third time with the output materialised: same result, pairs of this rank
     pairs = torch.full((2 * (res[0][0] + 8),), -1, dtype=torch.int64, device=f"cuda:{rank}")
     assert hj.join(pairs=pairs).astuple() == res[0]
     np.save(os.path.join(out_dir, f"pairs{rank}.npy"), pairs.cpu().numpy().view(np.uint64)[: 2 * res[0][0]].reshape(-1, 2))
     assert int((pairs[2 * res[0][0]:] != -1).sum()) == 0
+    assert host_res == res[0]
     np.save(os.path.join(out_dir, f"rank{rank}.npy"), np.array(res, dtype=np.uint64))
     # per-rank histogram getters must agree with the all-gathered view
     np.save(os.path.join(out_dir, f"ghist{rank}.npy"), hj.ctx.get_global_histogram(0))
@@ -90,6 +100,7 @@ def _worker_config(rank, world, port, shape, log2n, out_dir):
     import torch
     import torch.distributed as dist
     rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    from tools import checksum as CK
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -106,8 +117,12 @@ def _worker_config(rank, world, port, shape, log2n, out_dir):
         ds = torch.empty(ns, dtype=torch.int64, device=dev)
         rhj.fill_perm(dr, 8, nr, rank * nr, NR, seed=31, start_rid=rank * nr)
         rhj.fill_perm(ds, 8, ns, rank * ns, NS, seed=32, modulo=NR, start_rid=rank * ns)
-        want = (NS, 16 * (NR * (NR - 1) // 2) & m64, 16 * (NR * (NR - 1) // 2) & m64, NS * (NS - 1) // 2 & m64)
-        tb, caps = 8, (2 * nr, 2 * ns)
+        closed = (NS, 16 * (NR * (NR - 1) // 2) & m64, 16 * (NR * (NR - 1) // 2) & m64, NS * (NS - 1) // 2 & m64)
+        # all five words, pairing included: unpack to {key, rid} pairs for the device-side checker
+        un = lambda t: torch.stack([t >> 32, t & 0xFFFFFFFF], dim=1).reshape(-1)
+        want = CK.expected_result(torch, dist, un(dr), nr, un(ds), ns, NR, world, rank, dev)
+        assert tuple(want[:4]) == closed, (want, closed)
+        tb, caps = 8, None
     else:  # "c4": Zipf(1)-like probe keys (P(k) ~ 1/k), unique build keys covering the whole domain;
         # "c4_balanced": the same with RHJ_FLAG_BALANCED_ASSIGNMENT
         n = 1 << log2n
@@ -126,11 +141,12 @@ def _worker_config(rank, world, port, shape, log2n, out_dir):
             u = torch.rand(min(step, n - b), device=dev, dtype=torch.float64, generator=g)
             keys[b:b + step] = torch.clamp(torch.floor(torch.exp(u * float(np.log(NR)))).to(torch.int64) - 1, 0, NR - 1)
         ds.view(-1, 2)[:, 1] = torch.arange(rank * n, (rank + 1) * n, device=dev)
-        ksum = keys.sum().reshape(1)  # int64 wrap-around = arithmetic modulo 2^64
-        dist.all_reduce(ksum)
-        # rid_R of the partner of key k is the position of k in the permutation: not closed-form -> not compared
-        want = (NS, int(ksum.item()) & m64, None, NS * (NS - 1) // 2 & m64)
-        tb, caps = 16, (2 * n, 2 * n)
+        # the ranks go through a fixed bijection, so that the hot keys are spread over the
+        # partitions and ranks instead of being keys 0, 1, 2, ... (oracle orc_fill_zipf does the same)
+        rhj.apply_perm(ds, n, 2, NR, seed=4177)
+        want = CK.expected_result(torch, dist, dr, n, ds, n, NR, world, rank, dev)
+        assert want[0] == NS and want[3] == NS * (NS - 1) // 2 & m64
+        tb, caps = 16, None  # exact window sizes from a histogram: skew needs no guess
     ri = rhj.Relation(dr, nr, NR, tb)
     ro = rhj.Relation(ds, ns, NS, tb)
     hj = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=rank, window_caps=caps)
@@ -144,16 +160,16 @@ def _worker_config(rank, world, port, shape, log2n, out_dir):
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    mine = torch.tensor([v - (1 << 64) if v >= (1 << 63) else v for v in r.astuple()[:4]], dtype=torch.int64, device=dev)
+    got = CK.reduce_result(torch, dist, r, world, dev)
     share = torch.tensor([r.matches], dtype=torch.int64, device=dev)
     shares = [torch.zeros_like(share) for _ in range(world)]
     dist.all_gather(shares, share)
-    dist.all_reduce(mine)
+    tm = hj.ctx.timings().asdict()
     if rank == 0:
-        got = tuple(int(x) & m64 for x in mine.tolist())
         import json
         with open(os.path.join(out_dir, "result.json"), "w") as f:
-            json.dump({"shape": shape, "world": world, "got": got, "want": want, "ms": float(ms.item()),
+            json.dump({"shape": shape, "world": world, "got": list(got), "want": list(want), "ms": float(ms.item()),
+                       "words": ["matches", "sum_key", "sum_rid_r", "sum_rid_s", "sum_mix"], "stages_us_rank0": tm,
                        "tuples_per_s": (NR + NS) / float(ms.item()) * 1e3,
                        "matches_per_rank": [int(s.item()) for s in shares]}, f)
     dist.barrier()
@@ -178,6 +194,5 @@ def test_baseline_configs_4_and_5_full_size_all_gpus(tmp_path, shape):
     if keep:
         os.makedirs(keep, exist_ok=True)
         json.dump(res, open(os.path.join(keep, f"config_{shape}_n{world}.json"), "w"))
-    for got, want in zip(res["got"], res["want"]):
-        if want is not None:
-            assert got == want
+    assert len(res["want"]) == 5 and None not in res["want"]
+    assert res["got"] == res["want"]

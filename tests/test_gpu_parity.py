@@ -145,6 +145,38 @@ def test_window_overflow_is_reported(rhj, oracle):
     run.close()
 
 
+def test_default_window_capacity_under_skew_is_refused_exact_sizes_pass(rhj, oracle):
+    """include/rhj.h, rhj_plan: the default window capacity (allocation_factor x local size) only holds for
+    near-uniform partitions.  Two ranks, every probe tuple in one partition: the owner's window overflows
+    -> RHJ_ERR_CAPACITY at rhj_get_result; with the exact sizes of rhj_host_offsets (what the reference
+    computes after its histogram phase, data/Window.cpp:160-178) the same join equals the oracle."""
+    cfg = rhj.make_config(4, 4, 28, True)
+    inner = [oracle.fill_perm(20000, r * 20000, 40000, seed=3) for r in range(2)]
+    outer = []
+    for r in range(2):
+        o = np.zeros(30000, oracle.TUPLE)
+        o["key"] = 4242
+        o["rid"] = np.arange(len(o)) + r * 30000
+        outer.append(o)
+    run = GpuRun(rhj, cfg, inner, outer, window_caps=(0, 0))
+    with pytest.raises(rhj.RhjError) as e:
+        run.run_all()
+    assert e.value.code == -4
+    run.close()
+    P = 16
+    caps = []
+    for rels in (inner, outer):
+        loc = np.ascontiguousarray(np.stack([oracle.local_histogram(t, ocfg(oracle, cfg)) for t in rels]))
+        ws = np.zeros(2, np.uint64)
+        rhj.lib().rhj_host_offsets(loc.ctypes.data, 2, 0, P, None, None, None, None, ws.ctypes.data)
+        caps.append(int(ws.max()))
+    run = GpuRun(rhj, cfg, inner, outer, window_caps=tuple(caps))
+    res = run.run_all()
+    want = oracle.join(inner, outer, ocfg(oracle, cfg))
+    assert [r.astuple() for r in res] == [w.astuple() for w in want]
+    run.close()
+
+
 def test_device_generator_matches_oracle(rhj, oracle):
     import torch
     n, dom = 100000, 77777
@@ -157,6 +189,18 @@ def test_device_generator_matches_oracle(rhj, oracle):
             assert np.array_equal(got, want.view(np.uint64))
         else:
             assert np.array_equal(got, (want["key"] << np.uint64(32)) | want["rid"])
+
+
+def test_apply_perm_matches_oracle(rhj, oracle):
+    """rhj_apply_perm == orc_perm (the bijection orc_fill_zipf sends its ranks through)."""
+    import torch
+    dom, seed = 123457, 4177
+    vals = np.random.default_rng(3).integers(0, dom, 50000).astype(np.uint64)
+    t = torch.from_numpy(np.stack([vals, np.arange(len(vals), dtype=np.uint64)], axis=1).view(np.int64).copy()).cuda()
+    rhj.apply_perm(t, len(vals), 2, dom, seed)
+    got = t.cpu().numpy().view(np.uint64).reshape(-1, 2)
+    want = np.array([oracle.lib().orc_perm(int(v), dom, seed) for v in vals], np.uint64)
+    assert np.array_equal(got[:, 0], want) and np.array_equal(got[:, 1], np.arange(len(vals), dtype=np.uint64))
 
 
 def test_zipf_outer(rhj, oracle):
