@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--loc-bits", type=int, default=0, help="local radix bits (0 = by GPU count)")
     ap.add_argument("--agg", action="store_true", help="warp-aggregated histogram atomics")
     ap.add_argument("--build-cap", type=int, default=0, help="build slice capacity (0 = library default)")
+    ap.add_argument("--overlap", type=int, default=-1, help="SMs of the outer network pass beside the inner local pass (-1 = by GPU count, 0 = off)")
     ap.add_argument("--debug-env", action="store_true", help="let the library read its RHJ_* ablation switches")
     return ap.parse_args()
 
@@ -314,7 +315,7 @@ def run_ours(args):
         if world == 1:
             ctx.join_async(d_inner, n, d_outer, n)
         else:
-            rhj.join_multi_rank(ctx, inner, outer)
+            rhj.join_multi_rank(ctx, inner, outer, overlap=None if args.overlap < 0 else args.overlap)
 
     from tools import checksum as CK
     m64 = CK.M64
@@ -415,7 +416,8 @@ def run_ours(args):
         def e2e_step():
             if world == 1:
                 return ctx.join_host(pin_i.ptr, n, pin_o.ptr, n)
-            rhj.join_multi_rank(ctx, inner, outer, host=(pin_i.ptr, pin_o.ptr))
+            rhj.join_multi_rank(ctx, inner, outer, host=(pin_i.ptr, pin_o.ptr),
+                                overlap=None if args.overlap < 0 else args.overlap)
             return ctx.result()
         r = e2e_step()  # warm-up
         barrier()

@@ -72,7 +72,7 @@ class Timings(C.Structure):
 
 class WindowHandle(C.Structure):
     _fields_ = [("ipc", C.c_ubyte * 64), ("inner_offset", C.c_uint64), ("outer_offset", C.c_uint64),
-                ("capacity_inner", C.c_uint64), ("capacity_outer", C.c_uint64)]
+                ("capacity_inner", C.c_uint64), ("capacity_outer", C.c_uint64), ("flags_offset", C.c_uint64)]
 
 
 # name -> (restype, argtypes); every symbol include/rhj.h declares
@@ -93,6 +93,7 @@ SYMBOLS = {
     "rhj_window_export": (_int, [_vp, C.POINTER(WindowHandle)]),
     "rhj_window_import": (_int, [_vp, _int, C.POINTER(WindowHandle)]),
     "rhj_window_set_peer": (_int, [_vp, _int, _vp, _vp]),
+    "rhj_exchange_has_flags": (_int, [_vp]),
     "rhj_window_get": (_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "rhj_histogram": (_int, [_vp, _vp, _u64, _vp, _u64, _vp]),
     "rhj_local_histogram_dev": (_vp, [_vp]),
@@ -237,6 +238,9 @@ class Context:
 
     def window_import(self, peer: int, wh: WindowHandle):
         check(lib().rhj_window_import(self.h, peer, C.byref(wh)))
+
+    def has_flags(self) -> bool:
+        return bool(lib().rhj_exchange_has_flags(self.h))
 
     def window_get(self):
         a, b = _vp(), _vp()

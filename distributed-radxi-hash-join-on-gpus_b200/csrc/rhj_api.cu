@@ -111,6 +111,10 @@ struct rhj_ctx {
   int reserve_sms = 0, tune_push_sms = 32;
 
   // peers (data/Window.cpp: target of MPI_Put)
+  uint32_t *d_flags = nullptr;           // [2][64] arrival flags written by the peers
+  uint64_t peer_flags[kMaxRanks] = {};   // the peers' flag arrays (0: none, e.g. ranks emulated on one device)
+  uint32_t epoch = 0;                    // joins started on this context; the value the flags carry
+  bool use_flags = false;
   uint64_t peer_window[2][kMaxRanks] = {};
   void *ipc_base[kMaxRanks] = {};
 
@@ -362,6 +366,7 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
   add(2 * NS * 4);                                 // sub_cnt
   add(NS * 8); add((uint64_t)nowned * 8); add(((uint64_t)nowned + 1) * 8);  // item_lstart, jcount, jstart
   add(16); add(5 * 8); add(4);                     // work counter + pair cursor, result, status
+  add(2 * 64 * 4);                                 // arrival flags
   add((NS + kItemSlack) * sizeof(ItemDesc));       // expanded build/probe work list
   if (staged) {                                    // send buffers + push lists of the staged exchange
     add(max_local[0] * 8); add(max_local[1] * 8);
@@ -454,6 +459,7 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (!rc) rc = carve(ctx, 2ull, &ctx->d_work);  // [0] work counter, [1] output cursor of rhj_build_probe_pairs
   if (!rc) rc = carve(ctx, 5ull, &ctx->d_result);
   if (!rc) rc = carve(ctx, 1ull, &ctx->d_status);
+  if (!rc) rc = carve(ctx, 2ull * 64, &ctx->d_flags);
   ctx->items_cap = NS + kItemSlack;
   if (!rc) rc = carve(ctx, ctx->items_cap, &ctx->d_items);
   if (ctx->staged_exchange) {
@@ -465,6 +471,8 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   if (rc) return rc;
   RHJ_CUDA(cudaMemset(ctx->d_status, 0, sizeof(int)));
   RHJ_CUDA(cudaMemset(ctx->d_result, 0, 5 * 8));
+  RHJ_CUDA(cudaMemset(ctx->d_flags, 0, 2 * 64 * 4));
+  RHJ_CUDA(cudaDeviceSynchronize());  // the flags are zero before any peer can learn their address
   ctx->peer_window[0][ctx->rank] = reinterpret_cast<uint64_t>(ctx->window[0]);
   ctx->peer_window[1][ctx->rank] = reinterpret_cast<uint64_t>(ctx->window[1]);
   ctx->planned = true;
@@ -487,6 +495,7 @@ extern "C" int rhj_window_export(rhj_ctx *ctx, rhj_window_handle *out) {
   out->outer_offset = reinterpret_cast<char *>(ctx->window[1]) - ctx->pool;
   out->capacity_inner = ctx->window_cap[0];
   out->capacity_outer = ctx->window_cap[1];
+  out->flags_offset = reinterpret_cast<char *>(ctx->d_flags) - ctx->pool;
   return RHJ_OK;
 }
 
@@ -504,6 +513,11 @@ extern "C" int rhj_window_import(rhj_ctx *ctx, int peer_rank, const rhj_window_h
   ctx->ipc_base[peer_rank] = base;
   ctx->peer_window[0][peer_rank] = reinterpret_cast<uint64_t>(static_cast<char *>(base) + handle->inner_offset);
   ctx->peer_window[1][peer_rank] = reinterpret_cast<uint64_t>(static_cast<char *>(base) + handle->outer_offset);
+  ctx->peer_flags[peer_rank] = reinterpret_cast<uint64_t>(static_cast<char *>(base) + handle->flags_offset);
+  // arrival flags replace the launcher's barrier once every peer's flag array is mapped
+  ctx->use_flags = true;
+  for (int r = 0; r < ctx->nranks; ++r)
+    if (r != ctx->rank && !ctx->peer_flags[r]) ctx->use_flags = false;
   return RHJ_OK;
 }
 
@@ -514,6 +528,8 @@ extern "C" int rhj_window_set_peer(rhj_ctx *ctx, int peer_rank, void *inner_wind
   ctx->peer_window[1][peer_rank] = reinterpret_cast<uint64_t>(outer_window_dev);
   return RHJ_OK;
 }
+
+extern "C" int rhj_exchange_has_flags(rhj_ctx *ctx) { return ctx && ctx->use_flags && !ctx->staged_exchange ? 1 : 0; }
 
 extern "C" int rhj_window_get(rhj_ctx *ctx, void **inner_window_dev, void **outer_window_dev) {
   if (!ctx || !ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
@@ -692,6 +708,7 @@ extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner
   ctx->input_n[1] = outer_n;
   for (int k = 0; k < 2; ++k) ctx->nchunks1[k] = (uint32_t)((ctx->input_n[k] + ctx->chunk1 - 1) / ctx->chunk1);
   ctx->local_planned = false;
+  ctx->epoch += 1;
   ctx->ev_valid[EV_H2D0] = ctx->staged_pending;  // h2d_us only when this join's inputs were staged
   ctx->staged_pending = false;
   for (int k = 0; k < 2; ++k) ctx->rel_partitioned[k] = ctx->rel_scattered[k] = ctx->wait_timed[k] = false;
@@ -790,6 +807,12 @@ extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) 
     RHJ_CHECK_LAUNCH("k_push");
     RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
   }
+  if (ctx->use_flags && !ctx->staged_exchange) {
+    FlagPeers fp{};
+    for (int r = 0; r < ctx->nranks; ++r) fp.addr[r] = ctx->peer_flags[r];
+    k_signal_peers<<<1, 64, 0, st>>>(fp, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)k, ctx->epoch);
+    RHJ_CHECK_LAUNCH("k_signal_peers");
+  }
   RHJ_CUDA(cudaEventRecord(ctx->ev_rel_net[k], st));
   ctx->rel_scattered[k] = true;
   if (ctx->rel_scattered[k ^ 1]) {
@@ -866,6 +889,12 @@ extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
   // SNETCOMPL (performance/Measurements.cpp:157-165): from here to the start of the local pass
   RHJ_CUDA(cudaEventRecord(ctx->ev_wait0[which], st));
   ctx->wait_timed[which] = true;
+  if (ctx->use_flags && !ctx->staged_exchange) {
+    // every peer's stores of this relation have landed once its flag shows this join's epoch
+    k_wait_peers<<<1, 64, 0, st>>>(ctx->d_flags, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)which, ctx->epoch,
+                                   5000000000ull, ctx->d_status);
+    RHJ_CHECK_LAUNCH("k_wait_peers");
+  }
   return RHJ_OK;
 }
 
@@ -1139,6 +1168,8 @@ extern "C" int rhj_get_result(rhj_ctx *ctx, rhj_result *out, void *stream) {
   RHJ_CUDA(cudaStreamSynchronize(st));
   if (status == kDevWindowOverflow)
     return fail(RHJ_ERR_CAPACITY, "a receive window is smaller than the tuples assigned to it; raise allocation_factor or the window capacity");
+  if (status == kDevPeerTimeout)
+    return fail(RHJ_ERR_STATE, "a peer rank did not finish its network pass within 5 s (arrival flag never set)");
   if (status != kDevOk) return fail(RHJ_ERR_CAPACITY, "device workspace bound exceeded (status %d)", status);
   out->matches = r[0];
   out->sum_key = r[1];

@@ -43,6 +43,7 @@ enum DevStatus : int {
   kDevOk = 0,
   kDevWindowOverflow = 1,
   kDevLocalOverflow = 2,
+  kDevPeerTimeout = 3,
 };
 
 // ---------------------------------------------------------------------------------
@@ -1794,6 +1795,48 @@ __global__ void k_fill_perm(void *tuples, uint64_t n, uint64_t first, PermParams
     } else {
       reinterpret_cast<uint64_t *>(tuples)[i] = (key << 32) | (rid & 0xFFFFFFFFull);
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// Arrival flags: the barrier between the network pass and the local pass
+// (operators/HashJoin.cpp:119-121, MPI_Barrier after MPI_Win_flush) without a collective.
+// After its scatter kernel of relation k a rank writes the join's epoch into slot [k][me] of
+// every peer's flag array (release at system scope: the full-line stores of the scatter kernel,
+// which completed earlier in the same stream, are visible before the flag is); before its local
+// pass of relation k a rank waits until every peer's slot shows the epoch.  One rank per GPU
+// only: ranks emulated on one device must not wait for kernels that are queued behind them.
+// ---------------------------------------------------------------------------------
+struct FlagPeers {
+  uint64_t addr[64];  // byte address of every rank's flag array u32[2][64]; 0 = no such peer
+};
+
+__global__ void k_signal_peers(FlagPeers peers, uint32_t nranks, uint32_t me, uint32_t which, uint32_t epoch) {
+  const uint32_t r = threadIdx.x;
+  if (r >= nranks || r == me || peers.addr[r] == 0) return;
+  uint32_t *flag = reinterpret_cast<uint32_t *>(peers.addr[r]) + which * 64 + me;
+  __threadfence_system();
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(epoch) : "memory");
+}
+
+__global__ void k_wait_peers(const uint32_t *flags, uint32_t nranks, uint32_t me, uint32_t which, uint32_t epoch,
+                             unsigned long long timeout_ns, int *status) {
+  const uint32_t r = threadIdx.x;
+  if (r >= nranks || r == me) return;
+  const uint32_t *flag = flags + which * 64 + r;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while (true) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if ((int32_t)(v - epoch) >= 0) break;
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) {
+      atomicMax(status, (int)kDevPeerTimeout);
+      break;
+    }
+    __nanosleep(200);
   }
 }
 

@@ -152,6 +152,7 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
     (rid_R, rid_S) pairs (rhj_build_probe_pairs).  `host` = (inner_host, outer_host): the relations
     are taken from host memory through rhj_stage_host_inputs instead of `inner.data`/`outer.data`.
     `overlap`: SMs of the outer relation's network pass (None = overlap_sms(nranks))."""
+    import os
     import torch
     import torch.distributed as dist
     if host is not None:
@@ -174,8 +175,12 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
         host_group = _host_barrier_group(group)
         token = torch.zeros(1, dtype=torch.int32, device=dev)
 
+        use_nccl_barrier = not ctx.has_flags() or bool(os.environ.get("RHJ_NCCL_BARRIER"))
+
         def barrier(which):
-            if host_group is not None:  # optional host-side barrier (RHJ_HOST_BARRIER)
+            if not use_nccl_barrier and host_group is None:
+                ctx.exchange_wait(which)  # waits for this rank's stores and for every peer's arrival flag
+            elif host_group is not None:  # optional host-side barrier (RHJ_HOST_BARRIER)
                 ctx.exchange_sync(which)
                 dist.barrier(group=host_group)
             else:

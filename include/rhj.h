@@ -109,6 +109,7 @@ typedef struct rhj_window_handle {
   uint64_t outer_offset;
   uint64_t capacity_inner; /* tuples */
   uint64_t capacity_outer;
+  uint64_t flags_offset;   /* byte offset of the rank's arrival flags (u32[2][64]) inside the pool */
 } rhj_window_handle;
 
 const char *rhj_last_error(void);
@@ -155,6 +156,14 @@ int rhj_window_import(rhj_ctx *ctx, int peer_rank, const rhj_window_handle *hand
 /* peer in this process (same or peer-enabled device): raw device pointers */
 int rhj_window_set_peer(rhj_ctx *ctx, int peer_rank, void *inner_window_dev, void *outer_window_dev);
 int rhj_window_get(rhj_ctx *ctx, void **inner_window_dev, void **outer_window_dev);
+/* 1 when every peer's window was imported through rhj_window_import (one rank per GPU): the network
+ * pass then ends by writing this join's number into an arrival flag inside every peer's pool, and
+ * rhj_exchange_wait makes `stream` wait (a one-block kernel) until all peers' flags for the relation
+ * show it -- the barrier of operators/HashJoin.cpp:119-121 without a collective; the launcher needs
+ * no barrier of its own between rhj_exchange_wait and rhj_local_partition_rel.  All ranks must run
+ * the same sequence of joins.  0 (ranks in one process via rhj_window_set_peer, or one rank): the
+ * launcher provides the barrier. */
+int rhj_exchange_has_flags(rhj_ctx *ctx);
 
 /* ---- the four tasks (tasks/Task.h:10-30), individually invocable ---------- */
 
