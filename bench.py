@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--agg", action="store_true", help="warp-aggregated histogram atomics")
     ap.add_argument("--build-cap", type=int, default=0, help="build slice capacity (0 = library default)")
     ap.add_argument("--overlap", type=int, default=-1, help="SMs of the outer network pass beside the inner local pass (-1 = by GPU count, 0 = off)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "staged", "direct"])
     ap.add_argument("--debug-env", action="store_true", help="let the library read its RHJ_* ablation switches")
     return ap.parse_args()
 
@@ -284,6 +285,7 @@ def run_ours(args):
     G = n * world                # global relation size
     flags = (rhj.FLAG_HIST_WARP_AGGREGATE if args.agg else 0) | (0 if args.no_e2e else rhj.FLAG_STAGE_HOST_INPUTS)
     flags |= rhj.FLAG_DEBUG_ENV if args.debug_env else 0
+    flags |= {"auto": 0, "staged": rhj.FLAG_STAGED_EXCHANGE, "direct": rhj.FLAG_DIRECT_EXCHANGE}[args.exchange]
     # radix bits: sub-partitions of ~4096 build tuples (one shared-memory table) need
     # log2(global size / 4096) bits in total; weak scaling adds log2(N) bits
     default_bits = {1: (8, 8), 2: (8, 9), 4: (9, 9), 8: (9, 10)}.get(world, (9, 10))
@@ -449,8 +451,10 @@ def run_ours(args):
                            "radix_bits": f"{net_bits} network + {loc_bits} local", "tuple_bytes": 16,
                            "l2": "inputs (8 GiB per GPU) are larger than L2; no flush needed",
                            "exchange": "none (1 GPU)" if world == 1 else
-                           "fused: the scatter kernel stores full 128-byte lines into the owners' windows over NVLink "
-                           "(CUDA IPC); outer network pass beside the inner local pass from 4 GPUs on"},
+                           ("send buffers pushed to the owners' windows as sequential runs over NVLink (CUDA IPC), group of "
+                            "chunks by group beside the scatter; arrival flags instead of a barrier" if ctx.is_staged() else
+                            "fused: the scatter kernel stores full 128-byte lines into the owners' windows over NVLink "
+                            "(CUDA IPC); arrival flags instead of a barrier")},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "roofline_nvlink": roofline_nvlink,
                 "stages": stages, "cpu_baseline": cpu,
                 "result": {"matches": G, "checksum_ok": True, "checksum_words": 5}, "parity": parity}

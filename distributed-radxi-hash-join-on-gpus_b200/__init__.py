@@ -44,6 +44,8 @@ FLAG_HIST_WARP_AGGREGATE = 1
 FLAG_STAGE_HOST_INPUTS = 2
 FLAG_BALANCED_ASSIGNMENT = 4
 FLAG_DEBUG_ENV = 8
+FLAG_STAGED_EXCHANGE = 16
+FLAG_DIRECT_EXCHANGE = 32
 
 
 def make_config(network_fanout_bits=5, local_fanout_bits=5, payload_bits=27, enable_two_level=False,
@@ -94,6 +96,7 @@ SYMBOLS = {
     "rhj_window_import": (_int, [_vp, _int, C.POINTER(WindowHandle)]),
     "rhj_window_set_peer": (_int, [_vp, _int, _vp, _vp]),
     "rhj_exchange_has_flags": (_int, [_vp]),
+    "rhj_exchange_is_staged": (_int, [_vp]),
     "rhj_window_get": (_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "rhj_histogram": (_int, [_vp, _vp, _u64, _vp, _u64, _vp]),
     "rhj_local_histogram_dev": (_vp, [_vp]),
@@ -238,6 +241,9 @@ class Context:
 
     def window_import(self, peer: int, wh: WindowHandle):
         check(lib().rhj_window_import(self.h, peer, C.byref(wh)))
+
+    def is_staged(self) -> bool:
+        return bool(lib().rhj_exchange_is_staged(self.h))
 
     def has_flags(self) -> bool:
         return bool(lib().rhj_exchange_has_flags(self.h))

@@ -162,6 +162,11 @@ static int validate_config(const rhj_config *c, int rank, int nranks) {
   return RHJ_OK;
 }
 
+static bool exchange_is_staged(const rhj_config *cfg, int nranks) {
+  if (nranks < 2 || (cfg->flags & RHJ_FLAG_DIRECT_EXCHANGE)) return false;
+  return nranks > 2 || (cfg->flags & RHJ_FLAG_STAGED_EXCHANGE) != 0;
+}
+
 // position of a rank's first partition in the owner-major partition list (k_plan_network)
 static uint32_t first_owned_slot(uint32_t P, int rank, int nranks) {
   const uint32_t q = P / nranks, m = P % nranks;
@@ -214,7 +219,12 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   // which stops fitting above 1024 bins; wider fan-outs run on the first-generation pair
   // (k_histogram + k_scatter: one staged tile, per-tile scan).
   c->tune_scatter = (c->P <= 1024 && (!cfg->enable_two_level || c->L <= 1024)) ? 3 : 0;
-  c->staged_exchange = false;
+  // Exchange: with two ranks the scatter kernel's full-line stores go straight into the peer's window;
+  // from three ranks on every SM would be storing single lines into hundreds of regions spread over all
+  // peers at once, which the links sustain at a fraction of their rate (measured on 8 GPUs: 135 GB/s per
+  // direction against 560 GB/s on two), so the remote partitions are gathered in a local send buffer and
+  // pushed as long sequential runs.
+  c->staged_exchange = exchange_is_staged(cfg, nranks);
   if (cfg->flags & RHJ_FLAG_DEBUG_ENV) {
     // Ablation switches; only read when the caller asks for them.
     if (const char *e = getenv("RHJ_SCATTER")) {
@@ -231,7 +241,6 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
     if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
     if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
     if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
-    if (getenv("RHJ_STAGED_EXCHANGE")) c->staged_exchange = nranks > 1;
     if (const char *e = getenv("RHJ_WC")) c->tune_wc_variant = atoi(e);
     if (const char *e = getenv("RHJ_WC_L2_NET")) c->tune_wc_l2_net = std::max(0, std::min(64, atoi(e)));
     if (const char *e = getenv("RHJ_WC_L2_LOC")) c->tune_wc_l2_loc = std::max(0, std::min(64, atoi(e)));
@@ -380,7 +389,7 @@ extern "C" uint64_t rhj_workspace_bytes(const rhj_config *cfg, int nranks, uint6
   if (!cfg || validate_config(cfg, 0, nranks)) return 0;
   Layout lay;
   uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
-  compute_layout(cfg, 0, nranks, ml, wc, false, false, &lay);  // rank 0 owns the most partitions
+  compute_layout(cfg, 0, nranks, ml, wc, false, exchange_is_staged(cfg, nranks), &lay);  // rank 0 owns the most partitions
   return lay.total;
 }
 
@@ -529,7 +538,8 @@ extern "C" int rhj_window_set_peer(rhj_ctx *ctx, int peer_rank, void *inner_wind
   return RHJ_OK;
 }
 
-extern "C" int rhj_exchange_has_flags(rhj_ctx *ctx) { return ctx && ctx->use_flags && !ctx->staged_exchange ? 1 : 0; }
+extern "C" int rhj_exchange_is_staged(rhj_ctx *ctx) { return ctx && ctx->staged_exchange ? 1 : 0; }
+extern "C" int rhj_exchange_has_flags(rhj_ctx *ctx) { return ctx && ctx->use_flags ? 1 : 0; }
 
 extern "C" int rhj_window_get(rhj_ctx *ctx, void **inner_window_dev, void **outer_window_dev) {
   if (!ctx || !ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
@@ -613,7 +623,8 @@ static bool wc_geometry(uint32_t nbins, WcGeometry *g) {
 
 template <class Source, class Map, int TPB, int IPT, int CFIX>
 static int launch_scatter_wc_t(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                               uint32_t ring, const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+                               uint32_t ring, const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st,
+                               uint32_t c_lo, uint32_t c_hi) {
   const size_t smem = scatter_wc_smem_bytes(nbins, ring, TPB);
   auto kern = k_scatter_wc<Source, Map, TPB, IPT, CFIX>;
   RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -622,16 +633,19 @@ static int launch_scatter_wc_t(rhj_ctx *ctx, const Source &src, const Map &cm, u
   if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
   per_sm = std::min(per_sm, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1);
   const uint32_t sms = (uint32_t)std::max(1, ctx->sm_count - ctx->reserve_sms);
-  const uint32_t grid = std::min<uint32_t>(grid_chunks, sms * (uint32_t)per_sm);
+  const uint32_t span = std::min(c_hi, grid_chunks) > c_lo ? std::min(c_hi, grid_chunks) - c_lo : 0u;
+  if (span == 0) return RHJ_OK;
+  const uint32_t grid = std::min<uint32_t>(span, sms * (uint32_t)per_sm);
   kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ring, chunk_off, bin_base, ctx->d_status,
-                                Source::kDigitFromValue ? ctx->tune_wc_l2_loc : ctx->tune_wc_l2_net);
+                                Source::kDigitFromValue ? ctx->tune_wc_l2_loc : ctx->tune_wc_l2_net, c_lo, c_hi);
   RHJ_CHECK_LAUNCH("k_scatter_wc");
   return RHJ_OK;
 }
 
 template <class Source, class Map>
 static int launch_scatter_wc(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                             const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st) {
+                             const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st, uint32_t c_lo,
+                             uint32_t c_hi) {
   WcGeometry g;
   if (!wc_geometry(nbins, &g)) return fail(RHJ_ERR_INVALID, "no ring geometry for %u bins", nbins);
 #ifdef RHJ_TUNE_VARIANTS
@@ -639,27 +653,28 @@ static int launch_scatter_wc(rhj_ctx *ctx, const Source &src, const Map &cm, uin
   if (nbins <= 256 && ctx->tune_wc_variant) {
     const uint32_t r32 = 32;
     switch (ctx->tune_wc_variant) {
-      case 1: return launch_scatter_wc_t<Source, Map, 256, 8, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st);
-      case 2: return launch_scatter_wc_t<Source, Map, 256, 8, 0>(ctx, src, cm, grid_chunks, nbins, r32, chunk_off, bin_base, st);
-      case 3: return launch_scatter_wc_t<Source, Map, 1024, 8, 96>(ctx, src, cm, grid_chunks, nbins, 96, chunk_off, bin_base, st);
-      case 4: return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st);
-      case 5: return launch_scatter_wc_t<Source, Map, 256, 4, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st);
+      case 1: return launch_scatter_wc_t<Source, Map, 256, 8, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st, c_lo, c_hi);
+      case 2: return launch_scatter_wc_t<Source, Map, 256, 8, 0>(ctx, src, cm, grid_chunks, nbins, r32, chunk_off, bin_base, st, c_lo, c_hi);
+      case 3: return launch_scatter_wc_t<Source, Map, 1024, 8, 96>(ctx, src, cm, grid_chunks, nbins, 96, chunk_off, bin_base, st, c_lo, c_hi);
+      case 4: return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st, c_lo, c_hi);
+      case 5: return launch_scatter_wc_t<Source, Map, 256, 4, 24>(ctx, src, cm, grid_chunks, nbins, 24, chunk_off, bin_base, st, c_lo, c_hi);
       default: break;
     }
   }
 #endif
-  if (g.cfix == 48) return launch_scatter_wc_t<Source, Map, 512, 8, 48>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
-  if (g.cfix == 24 && g.tpb == 512) return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
-  if (g.cfix == 24) return launch_scatter_wc_t<Source, Map, 1024, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
-  return launch_scatter_wc_t<Source, Map, 512, 8, 0>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st);
+  if (g.cfix == 48) return launch_scatter_wc_t<Source, Map, 512, 8, 48>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st, c_lo, c_hi);
+  if (g.cfix == 24 && g.tpb == 512) return launch_scatter_wc_t<Source, Map, 512, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st, c_lo, c_hi);
+  if (g.cfix == 24) return launch_scatter_wc_t<Source, Map, 1024, 4, 24>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st, c_lo, c_hi);
+  return launch_scatter_wc_t<Source, Map, 512, 8, 0>(ctx, src, cm, grid_chunks, nbins, g.ring, chunk_off, bin_base, st, c_lo, c_hi);
 }
 
 template <class Source, class Map>
 static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
                           const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
-                          const uint64_t *bin_base, cudaStream_t st) {
+                          const uint64_t *bin_base, cudaStream_t st, uint32_t c_lo = 0, uint32_t c_hi = 0xFFFFFFFFu) {
   if (grid_chunks == 0) return RHJ_OK;
-  if (ctx->tune_scatter == 3) return launch_scatter_wc(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st);
+  if (ctx->tune_scatter == 3)
+    return launch_scatter_wc(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st, c_lo, c_hi);
   if (ctx->tune_scatter == 2) {
     if (ctx->tune_tpb == 1024)
       return launch_scatter3<Source, Map, 1024>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
@@ -781,38 +796,50 @@ extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int k = which;
   ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
-  int rc;
+  int rc = RHJ_OK;
   const int saved_reserve = ctx->reserve_sms;
-  // staged exchange: while the outer relation is scattered, the inner relation's push runs on the SMs left free
-  if (ctx->staged_exchange && k == 1) ctx->reserve_sms = std::max(ctx->reserve_sms, ctx->tune_push_sms);
-  if (ctx->cfg.tuple_bytes == 16) {
-    InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-    rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
-  } else {
-    InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-    rc = launch_scatter(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st);
+  // Staged exchange: the relation is scattered in a few groups of chunks, and every group's share of the
+  // remote partitions' runs is pushed to the owners on the side stream while the next group is scattered
+  // (runs are contiguous per partition and group, so the peers see long sequential writes).  From the
+  // second group on -- and for the outer relation from the start, its pushes queue behind the inner
+  // relation's -- the scatter leaves the push its SMs.
+  const uint32_t nch = ctx->nchunks1[k];
+  const uint32_t groups = (ctx->staged_exchange && ctx->tune_scatter == 3) ? std::max(1u, std::min(4u, nch / 256)) : 1u;
+  for (uint32_t g = 0; g < groups && !rc; ++g) {
+    const uint32_t c_lo = (uint32_t)((uint64_t)nch * g / groups), c_hi = (uint32_t)((uint64_t)nch * (g + 1) / groups);
+    if (ctx->staged_exchange && (k == 1 || g > 0)) ctx->reserve_sms = std::max(saved_reserve, ctx->tune_push_sms);
+    if (ctx->cfg.tuple_bytes == 16) {
+      InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+      rc = launch_scatter(ctx, src, cm, nch, ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, c_lo, groups > 1 ? c_hi : 0xFFFFFFFFu);
+    } else {
+      InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
+      rc = launch_scatter(ctx, src, cm, nch, ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, c_lo, groups > 1 ? c_hi : 0xFFFFFFFFu);
+    }
+    if (rc) break;
+    if (ctx->staged_exchange) {
+      RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
+      RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
+      const uint32_t push_ctas = (uint32_t)std::max(8, ctx->tune_push_sms * 8);
+      const uint32_t *row_lo = g == 0 ? nullptr : ctx->chunk1_hist[k] + (uint64_t)c_lo * ctx->P;
+      const uint32_t *row_hi = g + 1 == groups ? nullptr : ctx->chunk1_hist[k] + (uint64_t)c_hi * ctx->P;
+      k_push<<<push_ctas, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P,
+                                                    ctx->d_push_dst + (uint64_t)k * ctx->P,
+                                                    ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->P, ctx->d_status, row_lo,
+                                                    row_hi);
+      RHJ_CHECK_LAUNCH("k_push");
+    }
   }
   ctx->reserve_sms = saved_reserve;
   if (rc) return rc;
-  if (ctx->staged_exchange) {
-    // push this relation's remote partitions on the side stream: the inner relation's push
-    // overlaps the scatter of the outer relation, the outer relation's push overlaps the
-    // local pass of the inner one (rhj_exchange_wait / rhj_local_partition_rel order the rest)
-    RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
-    RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
-    const uint32_t push_ctas = (uint32_t)std::max(8, ctx->tune_push_sms * 8);
-    k_push<<<push_ctas, kPushTPB, 0, ctx->side>>>(ctx->d_push_src + (uint64_t)k * ctx->P,
-                                                  ctx->d_push_dst + (uint64_t)k * ctx->P,
-                                                  ctx->d_push_cnt + (uint64_t)k * ctx->P, ctx->P, ctx->d_status);
-    RHJ_CHECK_LAUNCH("k_push");
-    RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
-  }
-  if (ctx->use_flags && !ctx->staged_exchange) {
+  if (ctx->use_flags) {
+    // after this rank's last store of the relation: scatter kernel (direct) or last push (staged)
+    cudaStream_t sig = ctx->staged_exchange ? ctx->side : st;
     FlagPeers fp{};
     for (int r = 0; r < ctx->nranks; ++r) fp.addr[r] = ctx->peer_flags[r];
-    k_signal_peers<<<1, 64, 0, st>>>(fp, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)k, ctx->epoch);
+    k_signal_peers<<<1, 64, 0, sig>>>(fp, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)k, ctx->epoch);
     RHJ_CHECK_LAUNCH("k_signal_peers");
   }
+  if (ctx->staged_exchange) RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
   RHJ_CUDA(cudaEventRecord(ctx->ev_rel_net[k], st));
   ctx->rel_scattered[k] = true;
   if (ctx->rel_scattered[k ^ 1]) {
@@ -884,12 +911,13 @@ extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
   if (!ctx->rel_scattered[which]) return fail(RHJ_ERR_STATE, "rhj_network_partition first");
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // `stream` may be another one than the network pass ran on
-  RHJ_CUDA(cudaStreamWaitEvent(st, ctx->staged_exchange ? ctx->ev_pushed[which] : ctx->ev_rel_net[which], 0));
-  // SNETCOMPL (performance/Measurements.cpp:157-165): from here to the start of the local pass
+  // SNETCOMPL (performance/Measurements.cpp:157-165): from here -- the stream has nothing else to do
+  // until this relation has landed everywhere -- to the start of the local pass
   RHJ_CUDA(cudaEventRecord(ctx->ev_wait0[which], st));
+  // this rank's own stores (`stream` may be another one than the network pass ran on)
+  RHJ_CUDA(cudaStreamWaitEvent(st, ctx->staged_exchange ? ctx->ev_pushed[which] : ctx->ev_rel_net[which], 0));
   ctx->wait_timed[which] = true;
-  if (ctx->use_flags && !ctx->staged_exchange) {
+  if (ctx->use_flags) {
     // every peer's stores of this relation have landed once its flag shows this join's epoch
     k_wait_peers<<<1, 64, 0, st>>>(ctx->d_flags, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)which, ctx->epoch,
                                    5000000000ull, ctx->d_status);

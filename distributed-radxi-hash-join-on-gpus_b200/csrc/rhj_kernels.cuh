@@ -500,7 +500,7 @@ template <class Source, class Map, int TPB, int IPT, int CFIX>
 __global__ void __launch_bounds__(TPB, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1)
     k_scatter_wc(const Source src, const Map cm, const uint32_t nbins, const uint32_t ring_tuples,
                  const uint32_t *__restrict__ chunk_off, const uint64_t *__restrict__ bin_base,
-                 const int *__restrict__ status, const int l2_ahead) {
+                 const int *__restrict__ status, const int l2_ahead, const uint32_t c_lo, const uint32_t c_hi) {
   using Raw = typename Source::Raw;
   constexpr uint32_t BATCH = TPB * IPT, NW = TPB / 32, M = wc_rebase<CFIX>();
   constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -526,9 +526,12 @@ __global__ void __launch_bounds__(TPB, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1)
   const uint32_t sa_ring = pin_u32(smem_u32(ring)), sa_word = pin_u32(smem_u32(word));
   const uint32_t sa_head = pin_u32(smem_u32(head)), sa_base = pin_u32(smem_u32(base));
 
-  const uint32_t nchunks = cm.count();
-  const uint32_t c_begin = (uint32_t)((uint64_t)blockIdx.x * nchunks / gridDim.x);
-  const uint32_t c_end = (uint32_t)((uint64_t)(blockIdx.x + 1) * nchunks / gridDim.x);
+  // this launch's chunks [c_lo, min(c_hi, all)) are cut into one contiguous run per CTA
+  const uint32_t c_all = cm.count();
+  const uint32_t c_top = c_hi < c_all ? c_hi : c_all;
+  const uint32_t nchunks = c_top > c_lo ? c_top - c_lo : 0u;
+  const uint32_t c_begin = c_lo + (uint32_t)((uint64_t)blockIdx.x * nchunks / gridDim.x);
+  const uint32_t c_end = c_lo + (uint32_t)((uint64_t)(blockIdx.x + 1) * nchunks / gridDim.x);
   if (c_begin >= c_end) return;
   for (uint32_t d = tid; d < nbins; d += TPB) {
     word[d] = 0;
@@ -973,23 +976,33 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
 // lines of the peer's memory: NVLink sees full-line writes instead of the 8-byte-granular
 // runs the scatter kernel would produce.
 // ---------------------------------------------------------------------------------
+// Many small CTAs (256 threads, 8 stores in flight per thread), eight per SM's worth of the SMs the
+// concurrent scatter or local-pass kernel leaves free (rhj_ctx::tune_push_sms).  What was measured on
+// 8 GPUs (256M x 256M per GPU, ms per join): this form 11.7; 32 CTAs of 1024 threads that own 32 SMs
+// 12.4 (the push itself drops to ~620 GB/s: NVLink wants more stores in flight than 32 SMs hold);
+// 148 CTAs of 128 threads beside a scatter kernel capped at 56 registers 13.9.
 constexpr int kPushTPB = 256;
+constexpr int kPushInFlight = 8;
 __global__ void __launch_bounds__(kPushTPB) k_push(const uint64_t *__restrict__ src_addr,
                                                     const uint64_t *__restrict__ dst_addr,
                                                     const uint64_t *__restrict__ cnt, const uint32_t nparts,
-                                                    const int *__restrict__ status) {
-  // Persistent and deliberately small grid (a few CTAs on the SMs the concurrent scatter or
-  // local-pass kernel leaves free): a push that floods every SM with resident CTAs starves
-  // whatever is launched next -- the barrier's NCCL kernel waited 0.7 ms for a slot.
+                                                    const int *__restrict__ status,
+                                                    const uint32_t *__restrict__ row_lo,
+                                                    const uint32_t *__restrict__ row_hi) {
   if (*status != kDevOk) return;
   constexpr uint32_t kSlice = 8192;  // tuples per work item (64 KB)
+  // row_lo / row_hi: exclusive per-chunk offsets (rows of the chunk matrix) that bound the part of every
+  // partition's run to copy -- the tuples of one group of chunks; nullptr = from the start / to the end
   for (uint32_t p = 0; p < nparts; ++p) {
-    const uint64_t n = cnt[p];
+    if (cnt[p] == 0) continue;
+    const uint64_t lo = row_lo ? row_lo[p] : 0, hi = row_hi ? row_hi[p] : cnt[p];
+    const uint64_t n = hi - lo;
     if (n == 0) continue;
-    const uint64_t *src = reinterpret_cast<const uint64_t *>(src_addr[p]);
-    uint64_t *dst = reinterpret_cast<uint64_t *>(dst_addr[p]);
+    const uint64_t src_a = src_addr[p] + lo * 8, dst_a = dst_addr[p] + lo * 8;
+    const uint64_t *src = reinterpret_cast<const uint64_t *>(src_a);
+    uint64_t *dst = reinterpret_cast<uint64_t *>(dst_a);
     // head: up to the first 128-byte boundary of the destination, then slices of whole lines
-    uint64_t head = ((128 - (dst_addr[p] & 127)) & 127) / 8;
+    uint64_t head = ((128 - (dst_a & 127)) & 127) / 8;
     if (head > n) head = n;
     if (blockIdx.x == p % gridDim.x && threadIdx.x < head) dst[threadIdx.x] = ld_stream_u64(src + threadIdx.x);
     const uint64_t nslices = (n - head + kSlice - 1) / kSlice;
@@ -997,13 +1010,13 @@ __global__ void __launch_bounds__(kPushTPB) k_push(const uint64_t *__restrict__ 
     for (uint64_t sl = (blockIdx.x + gridDim.x - p % gridDim.x) % gridDim.x; sl < nslices; sl += gridDim.x) {
       const uint64_t b = head + sl * kSlice;
       const uint64_t e = b + kSlice < n ? b + kSlice : n;
-      for (uint64_t i = b + threadIdx.x; i < e; i += (uint64_t)kPushTPB * 8) {
-        uint64_t v[8];
+      for (uint64_t i = b + threadIdx.x; i < e; i += (uint64_t)kPushTPB * kPushInFlight) {
+        uint64_t v[kPushInFlight];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+        for (int u = 0; u < kPushInFlight; ++u)
           if (i + (uint64_t)u * kPushTPB < e) v[u] = ld_stream_u64(src + i + (uint64_t)u * kPushTPB);
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+        for (int u = 0; u < kPushInFlight; ++u)
           if (i + (uint64_t)u * kPushTPB < e) st_stream_u64(dst + i + (uint64_t)u * kPushTPB, v[u]);
       }
     }

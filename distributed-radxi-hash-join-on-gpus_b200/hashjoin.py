@@ -142,7 +142,7 @@ def overlap_sms(nranks: int, sm_count: int = 148) -> int:
     beside it (0 = no overlap).  With two ranks half of the tuples stay at home and the pass is
     HBM-bound like the local pass, so running them side by side gains nothing; from four ranks on
     the pass waits for NVLink and half of the SMs are enough to keep the links busy."""
-    return 0 if nranks < 4 else sm_count // 2
+    return 0 if nranks < 3 else sm_count // 2
 
 
 def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=None, capacity=None, host=None,
@@ -187,23 +187,31 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
                 ctx.exchange_wait(which)
                 dist.all_reduce(token, group=group)
 
-        sms = overlap_sms(ctx.nranks) if overlap is None else overlap
+        staged = ctx.is_staged()
+        if overlap is None:
+            sms = overlap_sms(ctx.nranks)
+        else:
+            sms = overlap
         if sms <= 0 or host_group is not None:
             ctx.network_partition()
             for which in (0, 1):
                 barrier(which)
                 ctx.local_partition_rel(which)
         else:
-            # The inner relation's barrier and local pass run on a second stream beside the outer
-            # relation's network pass, each on its share of the SMs.
+            # The inner relation's wait and local pass run on a second stream beside the outer
+            # relation's network pass.  Direct exchange: each gets its share of the SMs (`sms` for the
+            # network pass).  Staged exchange: the pushes (library side stream) hold their own SMs, the
+            # two passes share the rest as the block scheduler hands them out.
             main, side = torch.cuda.current_stream(), _side_stream(ctx)
             ctx.network_partition_rel(0)
             side.wait_stream(main)
-            ctx.set_sm_limit(sms)
+            if not staged:
+                ctx.set_sm_limit(sms)
             ctx.network_partition_rel(1)
             with torch.cuda.stream(side):
                 barrier(0)
-                ctx.set_sm_limit(ctx.sm_count() - sms)
+                if not staged:
+                    ctx.set_sm_limit(ctx.sm_count() - sms)
                 ctx.local_partition_rel(0)
             ctx.set_sm_limit(0)
             barrier(1)

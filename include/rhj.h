@@ -67,6 +67,12 @@ typedef struct rhj_config {
 /* Development only: rhj_init also reads the RHJ_* ablation switches from the environment
  * (DESIGN.md section 4).  Without this flag the library never calls getenv. */
 #define RHJ_FLAG_DEBUG_ENV 8u
+/* Exchange of the network pass (all ranks alike).  Default: two ranks store full 128-byte lines
+ * straight into the peer's window from the scatter kernel; three or more gather the remote
+ * partitions in a local send buffer and push them to the owners as long sequential runs, group of
+ * chunks by group of chunks, beside the scatter.  These flags force one or the other. */
+#define RHJ_FLAG_STAGED_EXCHANGE 16u
+#define RHJ_FLAG_DIRECT_EXCHANGE 32u
 
 /* Join result: the reference only counts (HashJoin::RESULT_COUNTER, operators/HashJoin.cpp:28,
  * tasks/BuildProbe.cpp:97-115).  The sums are an order-independent checksum over
@@ -164,6 +170,8 @@ int rhj_window_get(rhj_ctx *ctx, void **inner_window_dev, void **outer_window_de
  * the same sequence of joins.  0 (ranks in one process via rhj_window_set_peer, or one rank): the
  * launcher provides the barrier. */
 int rhj_exchange_has_flags(rhj_ctx *ctx);
+/* 1 when this context exchanges through send buffers + pushes (see RHJ_FLAG_STAGED_EXCHANGE). */
+int rhj_exchange_is_staged(rhj_ctx *ctx);
 
 /* ---- the four tasks (tasks/Task.h:10-30), individually invocable ---------- */
 

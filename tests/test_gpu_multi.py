@@ -42,6 +42,9 @@ def _worker(rank, world, port, per, knobs, out_dir):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     inner, outer = O.generate_reference(world, per, per)
     cfg = rhj.make_config(knobs[0], knobs[1], knobs[2], bool(knobs[3]))
+    if len(knobs) > 4:  # the exchange of three and more ranks (send buffers + pushes) on two
+        cfg.flags |= rhj.FLAG_STAGED_EXCHANGE
+        cfg.chunk_tuples = 8192  # many chunks: the relation is scattered and pushed in several groups
     ri = rhj.Relation.from_numpy(inner[rank], per * world, device=rank)
     ro = rhj.Relation.from_numpy(outer[rank], per * world, device=rank)
     cfg.flags |= rhj.FLAG_STAGE_HOST_INPUTS
@@ -69,15 +72,15 @@ def _worker(rank, world, port, per, knobs, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("knobs", [(5, 5, 27, 1), (8, 8, 24, 1), (5, 5, 27, 0)])
+@pytest.mark.parametrize("knobs", [(5, 5, 27, 1), (8, 8, 24, 1), (5, 5, 27, 0), (8, 8, 24, 1, "staged")])
 def test_two_gpus_nccl_ipc(oracle, tmp_path, knobs):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     import torch.multiprocessing as mp
-    world, per = 2, 150000 if knobs[3] else 20000
+    world, per = 2, (150000 if len(knobs) == 4 else 4600000) if knobs[3] else 20000
     mp.spawn(_worker, args=(world, _free_port(), per, knobs, str(tmp_path)), nprocs=world, join=True)
-    cfg = oracle.Config(*knobs)
+    cfg = oracle.Config(*knobs[:4])
     inner, outer = oracle.generate_reference(world, per, per)
     want, want_pairs = oracle.join_pairs(inner, outer, cfg, world * per)
     glob = sum(oracle.local_histogram(t, cfg) for t in inner)
