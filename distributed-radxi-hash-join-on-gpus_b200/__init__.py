@@ -100,6 +100,8 @@ SYMBOLS = {
     "rhj_window_get": (_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "rhj_histogram": (_int, [_vp, _vp, _u64, _vp, _u64, _vp]),
     "rhj_local_histogram_dev": (_vp, [_vp]),
+    "rhj_histogram_rel": (_int, [_vp, _int, _vp, _u64, _vp]),
+    "rhj_compute_offsets_rel": (_int, [_vp, _int, _vp, _vp]),
     "rhj_compute_offsets": (_int, [_vp, _vp, _vp]),
     "rhj_get_assignment": (_int, [_vp, _vp, _vp]),
     "rhj_get_local_histogram": (_int, [_vp, _int, _vp, _vp]),
@@ -259,6 +261,12 @@ class Context:
     # ---- stages (tasks/Task.h:10-30)
     def histogram(self, inner, inner_n: int, outer, outer_n: int):
         check(lib().rhj_histogram(self.h, _ptr(inner), inner_n, _ptr(outer), outer_n, _stream()))
+
+    def histogram_rel(self, which: int, rel, n: int):
+        check(lib().rhj_histogram_rel(self.h, which, _ptr(rel), n, _stream()))
+
+    def compute_offsets_rel(self, which: int, gathered=None):
+        check(lib().rhj_compute_offsets_rel(self.h, which, _ptr(gathered), _stream()))
 
     def local_histogram_ptr(self) -> int:
         return lib().rhj_local_histogram_dev(self.h)

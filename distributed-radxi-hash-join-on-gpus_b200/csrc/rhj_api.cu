@@ -105,6 +105,7 @@ struct rhj_ctx {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_scattered[2] = {nullptr, nullptr}, ev_pushed[2] = {nullptr, nullptr};
   bool rel_partitioned[2] = {false, false}, rel_scattered[2] = {false, false}, wait_timed[2] = {false, false};
+  bool hist_done[2] = {false, false}, offsets_done[2] = {false, false};
   cudaEvent_t ev_rel_net[2] = {nullptr, nullptr}, ev_rel_local[2] = {nullptr, nullptr};
   cudaEvent_t ev_wait0[2] = {nullptr, nullptr}, ev_wait1[2] = {nullptr, nullptr};
   bool staged_exchange = false;
@@ -127,16 +128,22 @@ struct rhj_ctx {
   cudaEvent_t ev[EV_COUNT] = {};
   bool ev_valid[EV_COUNT] = {};
   bool staged_pending = false;  // rhj_stage_host_inputs ran since the last rhj_histogram
+  bool h2d_pipelined = false;   // the last join's inputs came through rhj_join_host's copy stream
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_piece[128] = {};
+  cudaEvent_t ev_h2d_done = nullptr;
 
   // kernel choice and ablation knobs (rhj_init; environment only with RHJ_FLAG_DEBUG_ENV)
   int tune_scatter = 3;  // 0 first generation, 2 offset-driven tiles, 3 write-combining rings (default)
   bool tune_legacy_bp = false;
   int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
   int tune_wc_variant = 0;
+  uint64_t tune_piece_bytes = 256ull << 20;  // host->device piece of rhj_join_host
   int tune_wc_l2_net = 4, tune_wc_l2_loc = 4;  // L2 prefetch distance of the ring scatter, quarter batches
   int tune_l2_ahead_net = 2;  // the network pass reads 16-byte tuples: two tiles ahead measured best (three for 8-byte values)
 };
 
+static void invalidate_plan(rhj_ctx *ctx);
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
 static int validate_config(const rhj_config *c, int rank, int nranks) {
@@ -190,6 +197,10 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   if (device < 0 || device >= ndev) return fail(RHJ_ERR_INVALID, "device %d outside [0,%d)", device, ndev);
   RHJ_CUDA(cudaSetDevice(device));
   rhj_ctx *c = new rhj_ctx();
+  struct Guard {  // a failed rhj_init leaves nothing behind
+    rhj_ctx *c;
+    ~Guard() { if (c) rhj_destroy(c); }
+  } guard{c};
   c->rank = rank;
   c->nranks = nranks;
   c->device = device;
@@ -242,6 +253,7 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
     if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
     if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
     if (const char *e = getenv("RHJ_WC")) c->tune_wc_variant = atoi(e);
+    if (const char *e = getenv("RHJ_H2D_PIECE_KB")) c->tune_piece_bytes = (uint64_t)std::max(1, atoi(e)) << 10;
     if (const char *e = getenv("RHJ_WC_L2_NET")) c->tune_wc_l2_net = std::max(0, std::min(64, atoi(e)));
     if (const char *e = getenv("RHJ_WC_L2_LOC")) c->tune_wc_l2_loc = std::max(0, std::min(64, atoi(e)));
   }
@@ -252,17 +264,28 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
       RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_pushed[k], cudaEventDisableTiming));
     }
   }
+  guard.c = nullptr;
   *out = c;
   return RHJ_OK;
+}
+
+// everything carved from the pool is gone: no stage of an earlier plan may run any more
+static void invalidate_plan(rhj_ctx *ctx) {
+  ctx->planned = false;
+  ctx->stage = 0;
+  ctx->local_planned = false;
+  for (int k = 0; k < 2; ++k)
+    ctx->hist_done[k] = ctx->offsets_done[k] = ctx->rel_scattered[k] = ctx->rel_partitioned[k] = false;
 }
 
 extern "C" int rhj_pool_free_all(rhj_ctx *ctx) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();  // kernels of the last join may still use the pool
   if (ctx->pool) cudaFree(ctx->pool);
   ctx->pool = nullptr;
   ctx->pool_bytes = ctx->pool_used = 0;
-  ctx->planned = false;
+  invalidate_plan(ctx);
   return RHJ_OK;
 }
 
@@ -284,6 +307,10 @@ extern "C" int rhj_destroy(rhj_ctx *ctx) {
     if (ctx->ev_pushed[k]) cudaEventDestroy(ctx->ev_pushed[k]);
   }
   if (ctx->side) cudaStreamDestroy(ctx->side);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  for (int i = 0; i < 128; ++i)
+    if (ctx->ev_piece[i]) cudaEventDestroy(ctx->ev_piece[i]);
+  if (ctx->ev_h2d_done) cudaEventDestroy(ctx->ev_h2d_done);
   delete ctx;
   return RHJ_OK;
 }
@@ -318,7 +345,7 @@ extern "C" int rhj_pool_get_memory(rhj_ctx *ctx, uint64_t bytes, void **out_dev)
 extern "C" int rhj_pool_reset(rhj_ctx *ctx) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   ctx->pool_used = 0;
-  ctx->planned = false;
+  invalidate_plan(ctx);
   return RHJ_OK;
 }
 
@@ -517,6 +544,10 @@ extern "C" int rhj_window_import(rhj_ctx *ctx, int peer_rank, const rhj_window_h
     return fail(RHJ_ERR_INVALID, "peer %d planned different window capacities", peer_rank);
   cudaIpcMemHandle_t h;
   memcpy(&h, handle->ipc, 64);
+  if (ctx->ipc_base[peer_rank]) {  // re-import (the peer planned anew): drop the earlier mapping
+    cudaIpcCloseMemHandle(ctx->ipc_base[peer_rank]);
+    ctx->ipc_base[peer_rank] = nullptr;
+  }
   void *base = nullptr;
   RHJ_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
   ctx->ipc_base[peer_rank] = base;
@@ -688,20 +719,81 @@ static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32
   return RHJ_OK;
 }
 
+// histogram of chunks [c_lo, c_hi) of relation k (tasks/HistogramComputation.cpp:63-76 -> LocalHistogram)
 template <int TB>
-static int histogram_inputs(rhj_ctx *ctx, cudaStream_t st) {
-  for (int k = 0; k < 2; ++k) {
-    InputSource<TB> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-    ChunkMapFlat cm{ctx->input_n[k], ctx->chunk1, ctx->nchunks1[k]};
-    int rc = launch_histogram(ctx, src, cm, ctx->nchunks1[k], ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k],
-                              ctx->tile1_start[k], st);
-    if (rc) return rc;
-    dim3 grid((ctx->P + 31) / 32, 1);
-    k_colscan<32><<<grid, 32 * 32, 0, st>>>(ctx->chunk1_hist[k], ctx->P, nullptr, ctx->nchunks1[k],
-                                             ctx->d_local_hist + (uint64_t)k * ctx->P, ctx->d_status);
-    RHJ_CHECK_LAUNCH("k_colscan");
-  }
+static int histogram_chunks(rhj_ctx *ctx, int k, uint32_t c_lo, uint32_t c_hi, cudaStream_t st) {
+  if (c_hi <= c_lo) return RHJ_OK;
+  const uint64_t first = (uint64_t)c_lo * ctx->chunk1;
+  InputSource<TB> src{static_cast<const char *>(ctx->input[k]) + first * TB, ctx->P - 1, ctx->cfg.network_fanout_bits,
+                      ctx->key_shift};
+  ChunkMapFlat cm{std::min<uint64_t>(ctx->input_n[k] - first, (uint64_t)(c_hi - c_lo) * ctx->chunk1), ctx->chunk1, c_hi - c_lo};
+  const uint64_t row = (uint64_t)c_lo * ctx->P;
+  const uint64_t trow = row * ctx->tiles_per_chunk;
+  return launch_histogram(ctx, src, cm, c_hi - c_lo, ctx->P, ctx->chunk1_hist[k] + row,
+                          ctx->tile1_off[k] ? ctx->tile1_off[k] + trow : nullptr,
+                          ctx->tile1_start[k] ? ctx->tile1_start[k] + trow : nullptr, st);
+}
+
+// per-chunk counts -> exclusive per-chunk offsets + the relation's local histogram
+static int histogram_scan(rhj_ctx *ctx, int k, cudaStream_t st) {
+  dim3 grid((ctx->P + 31) / 32, 1);
+  k_colscan<32><<<grid, 32 * 32, 0, st>>>(ctx->chunk1_hist[k], ctx->P, nullptr, ctx->nchunks1[k],
+                                           ctx->d_local_hist + (uint64_t)k * ctx->P, ctx->d_status);
+  RHJ_CHECK_LAUNCH("k_colscan");
+  ctx->hist_done[k] = true;
+  if (ctx->hist_done[k ^ 1]) ctx->stage = std::max(ctx->stage, 1);
   return RHJ_OK;
+}
+
+// A new join starts with its inner relation: per-join state, start event, result and status words.
+static int begin_join(rhj_ctx *ctx, cudaStream_t st) {
+  ctx->local_planned = false;
+  ctx->epoch += 1;
+  ctx->ev_valid[EV_H2D0] = ctx->staged_pending;  // h2d_us only when this join's inputs were staged
+  ctx->staged_pending = false;
+  ctx->h2d_pipelined = false;
+  ctx->stage = 0;
+  for (int k = 0; k < 2; ++k) {
+    ctx->rel_partitioned[k] = ctx->rel_scattered[k] = ctx->wait_timed[k] = false;
+    ctx->hist_done[k] = ctx->offsets_done[k] = false;
+    ctx->input[k] = nullptr;
+    ctx->input_n[k] = 0;
+    ctx->nchunks1[k] = 0;
+  }
+  int rc = record(ctx, EV_START, st);
+  if (rc) return rc;
+  RHJ_CUDA(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), st));
+  RHJ_CUDA(cudaMemsetAsync(ctx->d_result, 0, 5 * 8, st));
+  return RHJ_OK;
+}
+
+static int set_input(rhj_ctx *ctx, int k, const void *dev, uint64_t n) {
+  if (n > ctx->max_local[k])
+    return fail(RHJ_ERR_INVALID, "relation %d: %llu tuples exceed the planned maximum %llu", k, (unsigned long long)n,
+                (unsigned long long)ctx->max_local[k]);
+  if (n && !dev) return fail(RHJ_ERR_INVALID, "NULL relation pointer");
+  if (reinterpret_cast<uintptr_t>(dev) & (ctx->cfg.tuple_bytes - 1))
+    return fail(RHJ_ERR_INVALID, "relations must be %u-byte aligned", ctx->cfg.tuple_bytes);
+  ctx->input[k] = dev;
+  ctx->input_n[k] = n;
+  ctx->nchunks1[k] = (uint32_t)((n + ctx->chunk1 - 1) / ctx->chunk1);
+  return RHJ_OK;
+}
+
+extern "C" int rhj_histogram_rel(rhj_ctx *ctx, int which, const void *rel_dev, uint64_t n, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (!ctx->planned) return fail(RHJ_ERR_STATE, "rhj_plan first");
+  if (which == 1 && !ctx->hist_done[0]) return fail(RHJ_ERR_STATE, "the inner relation's histogram starts a join: rhj_histogram_rel(0) first");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = RHJ_OK;
+  if (which == 0) rc = begin_join(ctx, st);
+  if (!rc) rc = set_input(ctx, which, rel_dev, n);
+  if (!rc) rc = ctx->cfg.tuple_bytes == 16 ? histogram_chunks<16>(ctx, which, 0, ctx->nchunks1[which], st)
+                                           : histogram_chunks<8>(ctx, which, 0, ctx->nchunks1[which], st);
+  if (!rc) rc = histogram_scan(ctx, which, st);
+  return rc;
 }
 
 extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *outer_dev,
@@ -715,41 +807,31 @@ extern "C" int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner
   if ((inner_n && !inner_dev) || (outer_n && !outer_dev)) return fail(RHJ_ERR_INVALID, "NULL relation pointer");
   if ((reinterpret_cast<uintptr_t>(inner_dev) | reinterpret_cast<uintptr_t>(outer_dev)) & (ctx->cfg.tuple_bytes - 1))
     return fail(RHJ_ERR_INVALID, "relations must be %u-byte aligned", ctx->cfg.tuple_bytes);
-  RHJ_CUDA(cudaSetDevice(ctx->device));
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  ctx->input[0] = inner_dev;
-  ctx->input[1] = outer_dev;
-  ctx->input_n[0] = inner_n;
-  ctx->input_n[1] = outer_n;
-  for (int k = 0; k < 2; ++k) ctx->nchunks1[k] = (uint32_t)((ctx->input_n[k] + ctx->chunk1 - 1) / ctx->chunk1);
-  ctx->local_planned = false;
-  ctx->epoch += 1;
-  ctx->ev_valid[EV_H2D0] = ctx->staged_pending;  // h2d_us only when this join's inputs were staged
-  ctx->staged_pending = false;
-  for (int k = 0; k < 2; ++k) ctx->rel_partitioned[k] = ctx->rel_scattered[k] = ctx->wait_timed[k] = false;
-  int rc = record(ctx, EV_START, st);
-  if (rc) return rc;
-  RHJ_CUDA(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), st));
-  RHJ_CUDA(cudaMemsetAsync(ctx->d_result, 0, 5 * 8, st));
-  rc = ctx->cfg.tuple_bytes == 16 ? histogram_inputs<16>(ctx, st) : histogram_inputs<8>(ctx, st);
-  if (rc) return rc;
-  ctx->stage = 1;
-  return RHJ_OK;
+  int rc = rhj_histogram_rel(ctx, 0, inner_dev, inner_n, stream);
+  if (!rc) rc = rhj_histogram_rel(ctx, 1, outer_dev, outer_n, stream);
+  return rc;
 }
 
 extern "C" uint64_t *rhj_local_histogram_dev(rhj_ctx *ctx) { return ctx ? ctx->d_local_hist : nullptr; }
 
-extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, void *stream) {
-  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
-  if (ctx->stage < 1) return fail(RHJ_ERR_STATE, "rhj_histogram first");
-  if (!gathered_dev && ctx->nranks > 1) return fail(RHJ_ERR_INVALID, "gathered histograms required when nranks > 1");
+// k_begin..k_end: relations planned by this launch; gathered: [nranks][2][P] (both) or [nranks][P] (one)
+static int plan_network(rhj_ctx *ctx, int k_begin, int k_end, const uint64_t *gathered_dev, bool one_relation_layout,
+                        cudaStream_t st) {
   for (int r = 0; r < ctx->nranks; ++r)
     if (!ctx->peer_window[0][r] || !ctx->peer_window[1][r])
       return fail(RHJ_ERR_STATE, "window of rank %d not imported (rhj_window_import / rhj_window_set_peer)", r);
-  RHJ_CUDA(cudaSetDevice(ctx->device));
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   PlanNetworkArgs a{};
-  a.gathered = gathered_dev ? gathered_dev : ctx->d_local_hist;
+  if (gathered_dev) {
+    a.gathered = gathered_dev;
+    a.rank_stride = one_relation_layout ? ctx->P : 2 * ctx->P;
+    a.rel_stride = one_relation_layout ? 0 : ctx->P;
+  } else {  // one rank: its own histograms, u64[2][P]
+    a.gathered = ctx->d_local_hist;
+    a.rank_stride = 2 * ctx->P;
+    a.rel_stride = ctx->P;
+  }
+  a.k_begin = k_begin;
+  a.k_end = k_end;
   a.nranks = ctx->nranks;
   a.rank = ctx->rank;
   a.parts = ctx->P;
@@ -780,10 +862,32 @@ extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, v
   a.push_cnt = ctx->d_push_cnt;
   k_plan_network<<<1, 1024, ((size_t)ctx->P + 1) * 8, st>>>(a);
   RHJ_CHECK_LAUNCH("k_plan_network");
-  int rc = record(ctx, EV_HIST, st);
-  if (rc) return rc;
-  ctx->stage = 2;
+  for (int k = k_begin; k < k_end; ++k) ctx->offsets_done[k] = true;
+  if (ctx->offsets_done[0] && ctx->offsets_done[1]) {
+    int rc = record(ctx, EV_HIST, st);
+    if (rc) return rc;
+    ctx->stage = std::max(ctx->stage, 2);
+  }
   return RHJ_OK;
+}
+
+extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (!ctx->hist_done[0] || !ctx->hist_done[1]) return fail(RHJ_ERR_STATE, "rhj_histogram first");
+  if (!gathered_dev && ctx->nranks > 1) return fail(RHJ_ERR_INVALID, "gathered histograms required when nranks > 1");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  return plan_network(ctx, 0, 2, gathered_dev, false, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int rhj_compute_offsets_rel(rhj_ctx *ctx, int which, const uint64_t *gathered_rel_dev, void *stream) {
+  if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
+  if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
+  if (!ctx->hist_done[which]) return fail(RHJ_ERR_STATE, "rhj_histogram_rel first");
+  if (!gathered_rel_dev && ctx->nranks > 1) return fail(RHJ_ERR_INVALID, "gathered histograms required when nranks > 1");
+  if (ctx->cfg.flags & RHJ_FLAG_BALANCED_ASSIGNMENT)
+    return fail(RHJ_ERR_STATE, "the size-balanced assignment needs both relations' histograms: use rhj_compute_offsets");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  return plan_network(ctx, which, which + 1, gathered_rel_dev, true, static_cast<cudaStream_t>(stream));
 }
 
 // One relation of the network pass.  Direct exchange (default): the scatter kernel's full-line
@@ -791,7 +895,7 @@ extern "C" int rhj_compute_offsets(rhj_ctx *ctx, const uint64_t *gathered_dev, v
 extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (which < 0 || which > 1) return fail(RHJ_ERR_INVALID, "which must be 0 (inner) or 1 (outer)");
-  if (!ctx->planned || ctx->stage < 2) return fail(RHJ_ERR_STATE, "rhj_compute_offsets first");
+  if (!ctx->planned || !ctx->offsets_done[which]) return fail(RHJ_ERR_STATE, "rhj_compute_offsets first");
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int k = which;
@@ -1044,7 +1148,7 @@ static int launch_build_probe_cap(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStr
 
 static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, bool emit, void *stream) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
-  if (ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
+  if (!ctx->planned || ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
   if (emit && pairs_cap > 0 && !pairs_dev) return fail(RHJ_ERR_INVALID, "pairs_dev is NULL");
   if (emit && (reinterpret_cast<uintptr_t>(pairs_dev) & 15)) return fail(RHJ_ERR_INVALID, "pairs_dev must be 16-byte aligned");
   RHJ_CUDA(cudaSetDevice(ctx->device));
@@ -1226,6 +1330,11 @@ extern "C" int rhj_get_timings(rhj_ctx *ctx, rhj_timings *out) {
   out->lp_us = us(EV_NET, EV_LOCAL);
   out->bp_us = us(EV_LOCAL, EV_BP);
   out->h2d_us = ctx->ev_valid[EV_H2D0] ? us(EV_H2D0, EV_START) : 0.0;
+  if (ctx->h2d_pipelined) {  // copies overlap the join: from the first byte's start to the last byte's arrival
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ctx->ev[EV_H2D0], ctx->ev_h2d_done) == cudaSuccess) out->h2d_us = (double)ms * 1000.0;
+    else cudaGetLastError();
+  }
   for (int k = 0; k < 2; ++k) {
     if (!ctx->wait_timed[k]) continue;
     float ms = 0;
@@ -1279,6 +1388,13 @@ extern "C" int rhj_stage_host_inputs(rhj_ctx *ctx, const void *inner_host, uint6
   return RHJ_OK;
 }
 
+// HashJoin::join() from host buffers, single rank, as a pipeline (first slice): the
+// relations cross PCIe in pieces on a copy stream, the histogram of a piece runs as soon as it has
+// arrived, and the inner relation is partitioned (network + local pass) while the outer relation is
+// still being copied.  What is left after the last byte has arrived is the outer relation's last
+// histogram piece, its two scatter passes and build/probe.
+static constexpr int kMaxPieces = 64;  // per relation
+
 extern "C" int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inner_n, const void *outer_host,
                              uint64_t outer_n, void *stream, rhj_result *out) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
@@ -1290,10 +1406,56 @@ extern "C" int rhj_join_host(rhj_ctx *ctx, const void *inner_host, uint64_t inne
     int rc = rhj_plan(ctx, inner_n, outer_n, 0, 0);
     if (rc) return rc;
   }
-  void *di = nullptr, *dout = nullptr;
-  int rc = rhj_stage_host_inputs(ctx, inner_host, inner_n, outer_host, outer_n, stream, &di, &dout);
-  if (rc) return rc;
-  return rhj_join(ctx, di, inner_n, dout, outer_n, stream, out);
+  if (inner_n > ctx->max_local[0] || outer_n > ctx->max_local[1])
+    return fail(RHJ_ERR_INVALID, "relation sizes exceed the planned maxima");
+  if ((inner_n && !inner_host) || (outer_n && !outer_host)) return fail(RHJ_ERR_INVALID, "NULL relation pointer");
+  RHJ_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!ctx->copy_stream) {
+    RHJ_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2 * kMaxPieces; ++i) RHJ_CUDA(cudaEventCreateWithFlags(&ctx->ev_piece[i], cudaEventDisableTiming));
+    RHJ_CUDA(cudaEventCreate(&ctx->ev_h2d_done));
+  }
+  const void *host[2] = {inner_host, outer_host};
+  const uint64_t n[2] = {inner_n, outer_n};
+  const uint32_t tb = ctx->cfg.tuple_bytes;
+  // the copies start once everything queued on `stream` so far is done (an earlier join may still read the buffers)
+  RHJ_CUDA(cudaEventRecord(ctx->ev[EV_H2D0], st));
+  RHJ_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev[EV_H2D0], 0));
+  uint32_t piece_chunks[2], npieces[2];
+  for (int k = 0; k < 2; ++k) {
+    const uint32_t nch = (uint32_t)((n[k] + ctx->chunk1 - 1) / ctx->chunk1);
+    // pieces of about 256 MB, at most kMaxPieces of them
+    const uint32_t want = std::max<uint32_t>(1, (uint32_t)(ctx->tune_piece_bytes / ((uint64_t)ctx->chunk1 * tb)));
+    piece_chunks[k] = std::max(want, (nch + kMaxPieces - 1) / kMaxPieces);
+    npieces[k] = (nch + piece_chunks[k] - 1) / piece_chunks[k];
+    for (uint32_t j = 0; j < npieces[k]; ++j) {
+      const uint64_t b = (uint64_t)j * piece_chunks[k] * ctx->chunk1;
+      const uint64_t e = std::min<uint64_t>(n[k], b + (uint64_t)piece_chunks[k] * ctx->chunk1);
+      RHJ_CUDA(cudaMemcpyAsync(static_cast<char *>(ctx->staged_input[k]) + b * tb, static_cast<const char *>(host[k]) + b * tb,
+                               (e - b) * tb, cudaMemcpyHostToDevice, ctx->copy_stream));
+      RHJ_CUDA(cudaEventRecord(ctx->ev_piece[k * kMaxPieces + j], ctx->copy_stream));
+    }
+  }
+  RHJ_CUDA(cudaEventRecord(ctx->ev_h2d_done, ctx->copy_stream));
+  ctx->staged_pending = true;
+  int rc = begin_join(ctx, st);
+  ctx->h2d_pipelined = true;
+  for (int k = 0; k < 2 && !rc; ++k) {
+    rc = set_input(ctx, k, ctx->staged_input[k], n[k]);
+    for (uint32_t j = 0; j < npieces[k] && !rc; ++j) {
+      RHJ_CUDA(cudaStreamWaitEvent(st, ctx->ev_piece[k * kMaxPieces + j], 0));
+      const uint32_t c_lo = j * piece_chunks[k], c_hi = std::min(ctx->nchunks1[k], c_lo + piece_chunks[k]);
+      rc = tb == 16 ? histogram_chunks<16>(ctx, k, c_lo, c_hi, st) : histogram_chunks<8>(ctx, k, c_lo, c_hi, st);
+    }
+    if (!rc) rc = histogram_scan(ctx, k, st);
+    if (!rc) rc = plan_network(ctx, k, k + 1, nullptr, false, st);
+    if (!rc) rc = rhj_network_partition_rel(ctx, k, stream);
+    if (!rc) rc = rhj_local_partition_rel(ctx, k, stream);
+  }
+  if (!rc) rc = rhj_build_probe(ctx, stream);
+  if (!rc && out) rc = rhj_get_result(ctx, out, stream);
+  return rc;
 }
 
 // -----------------------------------------------------------------------------------

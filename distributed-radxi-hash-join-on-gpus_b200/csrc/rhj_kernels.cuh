@@ -777,7 +777,9 @@ __global__ void __launch_bounds__(WARPS * 32) k_colscan(uint32_t *__restrict__ m
 // Also lays out the work of the later stages for the partitions this rank owns.
 // ---------------------------------------------------------------------------------
 struct PlanNetworkArgs {
-  const uint64_t *gathered;  // [nranks][2][P]
+  const uint64_t *gathered;  // [nranks][2][P], or [nranks][P] of one relation (rank_stride, rel_stride below)
+  uint32_t rank_stride, rel_stride;  // element (r, k, p) = gathered[r * rank_stride + k * rel_stride + p]
+  int k_begin, k_end;                // relations planned by this launch
   uint32_t nranks, rank, parts;
   uint64_t window_cap[2];
   uint64_t peer_window[2][64];  // byte address of every rank's window, per relation
@@ -814,11 +816,14 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
   const uint32_t q = P / n, m = P % n;  // owner r holds q + (r < m) partitions
   auto first_slot = [&](uint32_t r) { return r * q + (r < m ? r : m); };
   // GlobalHistogram.cpp:37-42 (sum over ranks) and OffsetMap.cpp:78-83 (exclusive scan over ranks)
-  for (int k = 0; k < 2; ++k)
+  auto local_count = [&](uint32_t r, int k, uint32_t p) -> uint64_t {
+    return a.gathered[(uint64_t)r * a.rank_stride + (uint64_t)k * a.rel_stride + p];
+  };
+  for (int k = a.k_begin; k < a.k_end; ++k)
     for (uint32_t p = tid; p < P; p += blockDim.x) {
       uint64_t g = 0, before = 0;
       for (uint32_t r = 0; r < n; ++r) {
-        uint64_t v = a.gathered[((uint64_t)r * 2 + k) * P + p];
+        uint64_t v = local_count(r, k, p);
         if (r < me) before += v;
         g += v;
       }
@@ -894,7 +899,7 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
     }
   }
   __syncthreads();
-  for (int k = 0; k < 2; ++k) {
+  for (int k = a.k_begin; k < a.k_end; ++k) {
     // OffsetMap.cpp:59-73: running sum per owner == exclusive scan in owner-major order
     uint64_t carry = 0;
     for (uint32_t i0 = 0; i0 < P; i0 += blockDim.x) {
@@ -949,7 +954,7 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
       uint64_t scarry = 0;
       for (uint32_t i0 = 0; i0 < P; i0 += blockDim.x) {
         const uint32_t i = i0 + tid;
-        const uint64_t v = (i < P && a.assignment[i] != me) ? a.gathered[((uint64_t)me * 2 + k) * P + i] : 0;
+        const uint64_t v = (i < P && a.assignment[i] != me) ? local_count(me, k, i) : 0;
         uint64_t total;
         const uint64_t ex = block_exclusive_scan<uint64_t>(v, tmp64, &total);
         if (i < P) sh_scan[i] = scarry + ex;
@@ -959,7 +964,7 @@ __global__ void __launch_bounds__(1024) k_plan_network(PlanNetworkArgs a) {
       for (uint32_t p = tid; p < P; p += blockDim.x) {
         const bool remote = a.assignment[p] != me;
         const uint64_t src = a.stage_base[k] + sh_scan[p] * 8;
-        a.push_cnt[k * P + p] = remote ? a.gathered[((uint64_t)me * 2 + k) * P + p] : 0;
+        a.push_cnt[k * P + p] = remote ? local_count(me, k, p) : 0;
         a.push_src[k * P + p] = src;
         a.push_dst[k * P + p] = a.dest[k * P + p];
         if (remote) a.dest[k * P + p] = src;  // the scatter kernel fills the send buffer instead

@@ -159,17 +159,36 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
         d_in, d_out = ctx.stage_host_inputs(host[0], inner.local_size, host[1], outer.local_size)
     else:
         d_in, d_out = inner.data, outer.data
-    ctx.histogram(d_in, inner.local_size, d_out, outer.local_size)
+    from . import FLAG_BALANCED_ASSIGNMENT
+    per_relation = ctx.nranks > 1 and ctx.is_staged() and not (ctx.cfg.flags & FLAG_BALANCED_ASSIGNMENT)
+    if not per_relation:
+        ctx.histogram(d_in, inner.local_size, d_out, outer.local_size)
     if ctx.nranks == 1:
         ctx.compute_offsets(None)
         ctx.network_partition()
         ctx.local_partition()
     else:
         dev = f"cuda:{ctx.device}"
-        local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr(), 2 * ctx.P), device=dev)
-        gathered = torch.empty(ctx.nranks * 2 * ctx.P, dtype=torch.int64, device=dev)
-        dist.all_gather_into_tensor(gathered, local, group=group)
-        ctx.compute_offsets(gathered)
+        if per_relation:
+            # Histogram, all-gather and offsets one relation at a time: the inner relation is already being
+            # scattered and pushed over NVLink while the outer relation's histogram is computed.
+            rels = ((d_in, inner.local_size), (d_out, outer.local_size))
+            for which in (0, 1):
+                if which == 1:
+                    ctx.set_sm_limit(ctx.sm_count() - 32)  # the pushes of the inner relation keep their SMs
+                ctx.histogram_rel(which, *rels[which])
+                ctx.set_sm_limit(0)
+                local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr() + which * ctx.P * 8, ctx.P), device=dev)
+                gathered = torch.empty(ctx.nranks * ctx.P, dtype=torch.int64, device=dev)
+                dist.all_gather_into_tensor(gathered, local, group=group)
+                ctx.compute_offsets_rel(which, gathered)
+                if which == 0:
+                    ctx.network_partition_rel(0)
+        else:
+            local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr(), 2 * ctx.P), device=dev)
+            gathered = torch.empty(ctx.nranks * 2 * ctx.P, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(gathered, local, group=group)
+            ctx.compute_offsets(gathered)
         # Per relation: my stores into the peers' windows are complete (exchange_wait), then
         # everybody's are (the all-reduce is the barrier of operators/HashJoin.cpp:119-121).
         host_group = _host_barrier_group(group)
@@ -193,7 +212,9 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
         else:
             sms = overlap
         if sms <= 0 or host_group is not None:
-            ctx.network_partition()
+            if not per_relation:
+                ctx.network_partition_rel(0)
+            ctx.network_partition_rel(1)
             for which in (0, 1):
                 barrier(which)
                 ctx.local_partition_rel(which)
@@ -203,7 +224,8 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
             # network pass).  Staged exchange: the pushes (library side stream) hold their own SMs, the
             # two passes share the rest as the block scheduler hands them out.
             main, side = torch.cuda.current_stream(), _side_stream(ctx)
-            ctx.network_partition_rel(0)
+            if not per_relation:
+                ctx.network_partition_rel(0)
             side.wait_stream(main)
             if not staged:
                 ctx.set_sm_limit(sms)

@@ -1,6 +1,7 @@
 // hpcjoin_b200.cpp -- see hpcjoin_b200.hpp.  Host-side sequencing only.
 #include "hpcjoin_b200.hpp"
 
+#include <unordered_map>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -293,7 +294,12 @@ void HistogramComputation::execute() {
   const uint64_t P = core::Configuration::NETWORK_PARTITIONING_COUNT();
   if (comm->size() > 1) {
     // one all-gather of u64[2][P] replaces MPI_Allreduce (GlobalHistogram.cpp:37) + MPI_Exscan (OffsetMap.cpp:78)
-    if (!gathered) gathered = memory::Pool::getMemory((uint64_t)comm->size() * 2 * P * 8);
+    // one gather buffer per context for all joins on it: this task object is built anew by every join(),
+    // and a bump allocation per join would exhaust the pool after a few of them
+    static std::unordered_map<rhj_ctx *, void *> buffers;
+    void *&slot = buffers[ctx];
+    if (!slot) slot = memory::Pool::getMemory((uint64_t)comm->size() * 2 * P * 8);
+    gathered = slot;
     comm->allgatherDevice(rhj_local_histogram_dev(ctx), gathered, 2 * P * 8, stream);
     check(rhj_compute_offsets(ctx, static_cast<const uint64_t *>(gathered), stream));
   } else {

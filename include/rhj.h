@@ -180,6 +180,13 @@ int rhj_exchange_is_staged(rhj_ctx *ctx);
 int rhj_histogram(rhj_ctx *ctx, const void *inner_dev, uint64_t inner_n, const void *outer_dev, uint64_t outer_n,
                   void *stream);
 uint64_t *rhj_local_histogram_dev(rhj_ctx *ctx);
+/* The same phase one relation at a time (which: 0 inner, 1 outer; the inner relation's call starts a new
+ * join), so that the stages of the inner relation can run while the outer relation is still on its way:
+ * host->device in rhj_join_host, or -- with several ranks -- crossing NVLink.  rhj_compute_offsets_rel
+ * takes that relation's gathered histograms, u64[nranks][P] in rank order (NULL with one rank); it is
+ * refused under RHJ_FLAG_BALANCED_ASSIGNMENT, whose rule needs both relations' histograms. */
+int rhj_histogram_rel(rhj_ctx *ctx, int which, const void *rel_dev, uint64_t n, void *stream);
+int rhj_compute_offsets_rel(rhj_ctx *ctx, int which, const uint64_t *gathered_rel_dev, void *stream);
 
 /* TASK_HISTOGRAM part 2 -- GlobalHistogram.cpp:31-48 (sum over ranks), AssignmentMap.cpp:34-49
  * (p % nranks), OffsetMap.cpp:59-93 (base / relative / absolute offsets), all on the device.

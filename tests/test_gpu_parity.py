@@ -136,6 +136,33 @@ def test_join_host_buffers(rhj, oracle):
     ctx.close()
 
 
+def test_join_host_pipeline_many_pieces(rhj, oracle, monkeypatch):
+    """rhj_join_host copies in pieces and partitions the inner relation while the outer one is still on its
+    way; with small pieces (ablation switch) every relation crosses in dozens of them, ragged tail included."""
+    monkeypatch.setenv("RHJ_H2D_PIECE_KB", "256")
+    cfg = rhj.make_config(6, 6, 26, True, chunk_tuples=8192, flags=rhj.FLAG_STAGE_HOST_INPUTS | rhj.FLAG_DEBUG_ENV)
+    inner = oracle.fill_perm(300001, 0, 300001, seed=5)
+    outer = oracle.fill_zipf(700003, 0, 300001, 1.0, seed=6)
+    want = oracle.join([inner], [outer], ocfg(oracle, cfg))[0].astuple()
+    ctx = rhj.Context(cfg)
+    pin_i, pin_o = rhj.PinnedBuffer(inner.nbytes), rhj.PinnedBuffer(outer.nbytes)
+    pin_i.array[:] = inner.view(np.uint8)
+    pin_o.array[:] = outer.view(np.uint8)
+    for _ in range(2):
+        assert ctx.join_host(pin_i.ptr, len(inner), pin_o.ptr, len(outer)).astuple() == want
+    t = ctx.timings()
+    assert t.h2d_us > 0 and t.jtotal_us >= t.h2d_us * 0.5
+    # device-resident inputs on the same context afterwards
+    import torch
+    di = torch.from_numpy(inner.view(np.int64).copy()).cuda()
+    do = torch.from_numpy(outer.view(np.int64).copy()).cuda()
+    assert ctx.join(di, len(inner), do, len(outer)).astuple() == want
+    assert ctx.timings().h2d_us == 0
+    ctx.close()
+    pin_i.free()
+    pin_o.free()
+
+
 def test_window_overflow_is_reported(rhj, oracle):
     inner, outer = oracle.generate_reference(1, 50000, 50000)
     run = GpuRun(rhj, rhj.make_config(4, 4, 28, True), inner, outer, window_caps=(1000, 1000))
