@@ -630,6 +630,60 @@ __global__ void __launch_bounds__(TPB, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1)
     }
   };
 
+  // flush(0) for narrow fan-outs (at most two bins per warp, i.e. the reference's shipped 32 partitions):
+  // every bin has several lines to give per batch, so eight lanes simply take one bin, read its state
+  // themselves (broadcast loads) and copy its lines -- no votes, no shuffles (-8 % on a 32-bin pass).
+  // With more bins per warp the vote of flush() wins: at 256 bins this form was measured 5 % slower,
+  // although it executes a third fewer instructions (bins without a full line idle their eight lanes).
+  auto flush_fast = [&]() {
+    const uint32_t gmask = 0xFFu << (sub * 8);
+    for (uint32_t i0 = 0; i0 < bpw; i0 += 4) {
+      const uint32_t idx = i0 + sub, bin = first + idx;
+      if (idx < bpw && bin < nbins) {
+        const uint32_t w32 = lds_u32(sa_word + bin * 4);
+        const uint32_t h = lds_u16(sa_head + bin * 2);
+        uint32_t t = w32 & 0xFFFFu;
+        const uint32_t lim = w32 >> 16;
+        uint32_t fb, nh;
+        if (t >= lim) {  // ring full (or overflowed): everything it holds goes out
+          fb = lim;
+          nh = t;
+        } else {
+          fb = t & ~15u;
+          if (fb < h) fb = h;
+          nh = fb;
+        }
+        if (nh != h) {
+          uint64_t b = lds_u64(sa_base + bin * 8);
+          const uint32_t sa_bin = sa_ring + bin * C * 8;
+          for (uint32_t ql = h & ~15u; ql < fb; ql += 16) {
+            const uint32_t q0 = ql + sub2;
+            if (h <= ql && ql + 16 <= fb) {
+              st_stream_v2(reinterpret_cast<void *>(b + (uint64_t)q0 * 8), lds_v2(sa_bin + slot(q0) * 8));
+            } else {
+              if (h <= q0 && q0 < fb)
+                st_stream_u64(reinterpret_cast<uint64_t *>(b + (uint64_t)q0 * 8), lds_u64(sa_bin + slot(q0) * 8));
+              if (h <= q0 + 1 && q0 + 1 < fb)
+                st_stream_u64(reinterpret_cast<uint64_t *>(b + (uint64_t)(q0 + 1) * 8), lds_u64(sa_bin + slot(q0 + 1) * 8));
+            }
+          }
+          __syncwarp(gmask);  // every lane of the group has read the bin's state before one of them replaces it
+          if ((lane & 7) == 0) {
+            if (nh >= M) {
+              const uint32_t k = (nh / M) * M;
+              nh -= k;
+              t -= k;
+              b += (uint64_t)k * 8;
+              sts_u64(sa_base + bin * 8, b);
+            }
+            sts_u32(sa_word + bin * 4, (((nh & ~15u) + C) << 16) | t);
+            sts_u16(sa_head + bin * 2, nh);
+          }
+        }
+      }
+    }
+  };
+
   auto load_raw = [&](const Raw *p, uint32_t n, Raw (&raw)[IPT]) {
     p += tid;
     if (n >= BATCH) {
@@ -695,7 +749,8 @@ __global__ void __launch_bounds__(TPB, TPB <= 256 ? 4 : TPB <= 512 ? 2 : 1)
   while (true) {
     const uint32_t n = (uint32_t)min((uint64_t)BATCH, ce - pos);
     __syncthreads();
-    flush(chunk_start ? 1 : 0, c, seg);
+    if (!chunk_start && bpw <= 2) flush_fast();
+    else flush(chunk_start ? 1 : 0, c, seg);
     __syncthreads();
     place(raw, n);
     pos += n;
