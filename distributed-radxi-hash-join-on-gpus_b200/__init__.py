@@ -66,7 +66,7 @@ class Result(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("jtotal_us", C.c_double), ("jhist_us", C.c_double), ("jmpi_us", C.c_double),
                 ("jproc_us", C.c_double), ("lp_us", C.c_double), ("bp_us", C.c_double), ("h2d_us", C.c_double),
-                ("snetcompl_us", C.c_double)]
+                ("snetcompl_us", C.c_double), ("push_us", C.c_double)]
 
     def asdict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -103,7 +103,7 @@ struct rhj_ctx {
   uint64_t *sendbuf[2] = {nullptr, nullptr};
   uint64_t *d_push_src = nullptr, *d_push_dst = nullptr, *d_push_cnt = nullptr;
   cudaStream_t side = nullptr;
-  cudaEvent_t ev_scattered[2] = {nullptr, nullptr}, ev_pushed[2] = {nullptr, nullptr};
+  cudaEvent_t ev_scattered[2] = {nullptr, nullptr}, ev_pushed[2] = {nullptr, nullptr}, ev_push_begin[2] = {nullptr, nullptr};
   bool rel_partitioned[2] = {false, false}, rel_scattered[2] = {false, false}, wait_timed[2] = {false, false};
   bool hist_done[2] = {false, false}, offsets_done[2] = {false, false};
   cudaEvent_t ev_rel_net[2] = {nullptr, nullptr}, ev_rel_local[2] = {nullptr, nullptr};
@@ -138,6 +138,7 @@ struct rhj_ctx {
   bool tune_legacy_bp = false;
   int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
   int tune_wc_variant = 0;
+  int tune_push_priority = 1;
   uint64_t tune_piece_bytes = 256ull << 20;  // host->device piece of rhj_join_host
   int tune_wc_l2_net = 4, tune_wc_l2_loc = 4;  // L2 prefetch distance of the ring scatter, quarter batches
   int tune_l2_ahead_net = 2;  // the network pass reads 16-byte tuples: two tiles ahead measured best (three for 8-byte values)
@@ -253,15 +254,21 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
     if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
     if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
     if (const char *e = getenv("RHJ_WC")) c->tune_wc_variant = atoi(e);
+    if (const char *e = getenv("RHJ_PUSH_PRIORITY")) c->tune_push_priority = atoi(e);
     if (const char *e = getenv("RHJ_H2D_PIECE_KB")) c->tune_piece_bytes = (uint64_t)std::max(1, atoi(e)) << 10;
     if (const char *e = getenv("RHJ_WC_L2_NET")) c->tune_wc_l2_net = std::max(0, std::min(64, atoi(e)));
     if (const char *e = getenv("RHJ_WC_L2_LOC")) c->tune_wc_l2_loc = std::max(0, std::min(64, atoi(e)));
   }
   if (c->staged_exchange) {
-    RHJ_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    // the pushes are what NVLink waits for: their CTAs are placed before those of a scatter or local-pass
+    // launch that becomes ready at the same time
+    int prio_lo = 0, prio_hi = 0;  // numerically lower = higher priority
+    RHJ_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    RHJ_CUDA(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, c->tune_push_priority ? prio_hi : prio_lo));
     for (int k = 0; k < 2; ++k) {
       RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_scattered[k], cudaEventDisableTiming));
-      RHJ_CUDA(cudaEventCreateWithFlags(&c->ev_pushed[k], cudaEventDisableTiming));
+      RHJ_CUDA(cudaEventCreate(&c->ev_pushed[k]));
+      RHJ_CUDA(cudaEventCreate(&c->ev_push_begin[k]));
     }
   }
   guard.c = nullptr;
@@ -305,6 +312,7 @@ extern "C" int rhj_destroy(rhj_ctx *ctx) {
     if (ctx->ev_wait1[k]) cudaEventDestroy(ctx->ev_wait1[k]);
     if (ctx->ev_scattered[k]) cudaEventDestroy(ctx->ev_scattered[k]);
     if (ctx->ev_pushed[k]) cudaEventDestroy(ctx->ev_pushed[k]);
+    if (ctx->ev_push_begin[k]) cudaEventDestroy(ctx->ev_push_begin[k]);
   }
   if (ctx->side) cudaStreamDestroy(ctx->side);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -923,6 +931,7 @@ extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) 
     if (ctx->staged_exchange) {
       RHJ_CUDA(cudaEventRecord(ctx->ev_scattered[k], st));
       RHJ_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_scattered[k], 0));
+      if (g == 0) RHJ_CUDA(cudaEventRecord(ctx->ev_push_begin[k], ctx->side));
       const uint32_t push_ctas = (uint32_t)std::max(8, ctx->tune_push_sms * 8);
       const uint32_t *row_lo = g == 0 ? nullptr : ctx->chunk1_hist[k] + (uint64_t)c_lo * ctx->P;
       const uint32_t *row_hi = g + 1 == groups ? nullptr : ctx->chunk1_hist[k] + (uint64_t)c_hi * ctx->P;
@@ -1333,6 +1342,12 @@ extern "C" int rhj_get_timings(rhj_ctx *ctx, rhj_timings *out) {
   if (ctx->h2d_pipelined) {  // copies overlap the join: from the first byte's start to the last byte's arrival
     float ms = 0;
     if (cudaEventElapsedTime(&ms, ctx->ev[EV_H2D0], ctx->ev_h2d_done) == cudaSuccess) out->h2d_us = (double)ms * 1000.0;
+    else cudaGetLastError();
+  }
+  if (ctx->staged_exchange && ctx->rel_scattered[0] && ctx->rel_scattered[1]) {
+    // NVLink window of the staged exchange: first push of the inner relation to last push of the outer one
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ctx->ev_push_begin[0], ctx->ev_pushed[1]) == cudaSuccess) out->push_us = (double)ms * 1000.0;
     else cudaGetLastError();
   }
   for (int k = 0; k < 2; ++k) {

@@ -105,6 +105,8 @@ typedef struct rhj_timings {
                           waiting for the network pass to complete on all ranks = sum over both relations of the
                           time between rhj_exchange_wait and the start of that relation's local pass (the launcher's
                           barrier lies in between); 0 with one rank.  Included in lp_us. */
+  double push_us;      /* staged exchange: from the first push of the inner relation to the end of the last push of
+                          the outer one on this rank (the time NVLink carries the join's remote tuples); else 0 */
 } rhj_timings;
 
 /* Peer-visible description of a rank's receive windows (replaces MPI_Win_create,

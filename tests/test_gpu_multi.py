@@ -44,6 +44,7 @@ def _worker(rank, world, port, per, knobs, out_dir):
     cfg = rhj.make_config(knobs[0], knobs[1], knobs[2], bool(knobs[3]))
     if len(knobs) > 4:  # the exchange of three and more ranks (send buffers + pushes) on two
         cfg.flags |= rhj.FLAG_STAGED_EXCHANGE
+        os.environ["RHJ_PER_RELATION_EXCHANGE"] = "1"  # and with the inner relation's histogram exchanged first
         cfg.chunk_tuples = 8192  # many chunks: the relation is scattered and pushed in several groups
     ri = rhj.Relation.from_numpy(inner[rank], per * world, device=rank)
     ro = rhj.Relation.from_numpy(outer[rank], per * world, device=rank)
