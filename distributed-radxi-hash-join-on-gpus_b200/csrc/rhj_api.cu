@@ -83,9 +83,6 @@ struct rhj_ctx {
   void *staged_input[2] = {nullptr, nullptr};
   uint32_t *chunk1_hist[2] = {nullptr, nullptr};
   uint32_t *chunk2_hist[2] = {nullptr, nullptr};
-  uint32_t *tile1_off[2] = {nullptr, nullptr}, *tile2_off[2] = {nullptr, nullptr};    // [row][bins]
-  uint16_t *tile1_start[2] = {nullptr, nullptr}, *tile2_start[2] = {nullptr, nullptr};
-  uint32_t tiles_per_chunk = 0;
   uint64_t *d_local_hist = nullptr, *d_global = nullptr, *d_base = nullptr, *d_rel = nullptr, *d_abs = nullptr,
            *d_dest = nullptr, *d_winsizes = nullptr;
   uint32_t *d_assign = nullptr;
@@ -134,14 +131,13 @@ struct rhj_ctx {
   cudaEvent_t ev_h2d_done = nullptr;
 
   // kernel choice and ablation knobs (rhj_init; environment only with RHJ_FLAG_DEBUG_ENV)
-  int tune_scatter = 3;  // 0 first generation, 2 offset-driven tiles, 3 write-combining rings (default)
+  int tune_scatter = 3;  // 0 first generation (k_scatter), 3 write-combining rings (default)
   bool tune_legacy_bp = false;
-  int tune_tpb = 1024, tune_l2_ahead = 3, tune_hist_rep = 4, tune_bp_tpb = 512;
+  int tune_bp_tpb = 512;
   int tune_wc_variant = 0;
   int tune_push_priority = 1;
   uint64_t tune_piece_bytes = 256ull << 20;  // host->device piece of rhj_join_host
   int tune_wc_l2_net = 4, tune_wc_l2_loc = 4;  // L2 prefetch distance of the ring scatter, quarter batches
-  int tune_l2_ahead_net = 2;  // the network pass reads 16-byte tuples: two tiles ahead measured best (three for 8-byte values)
 };
 
 static void invalidate_plan(rhj_ctx *ctx);
@@ -166,7 +162,7 @@ static int validate_config(const rhj_config *c, int rank, int nranks) {
   if (cap != 1024 && cap != 2048 && cap != 4096 && cap != 5120 && cap != 8192)
     return fail(RHJ_ERR_INVALID, "build_capacity must be 1024, 2048, 4096, 5120 or 8192");
   uint32_t chunk = c->chunk_tuples ? c->chunk_tuples : kDefaultChunk;
-  if (chunk % kTile != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kTile);
+  if (chunk % kChunkGranule != 0) return fail(RHJ_ERR_INVALID, "chunk_tuples must be a multiple of %d", kChunkGranule);
   return RHJ_OK;
 }
 
@@ -216,7 +212,6 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   c->chunk1 = c->chunk2 = cfg->chunk_tuples ? cfg->chunk_tuples : kDefaultChunk;
   c->cap_r = cfg->build_capacity ? cfg->build_capacity : kDefaultBuildCap;
   c->sslice = 4 * c->cap_r;
-  c->tiles_per_chunk = c->chunk1 / kTile;
   cudaDeviceProp prop;
   RHJ_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
@@ -239,17 +234,8 @@ extern "C" int rhj_init(rhj_ctx **out, int rank, int nranks, int device, const r
   c->staged_exchange = exchange_is_staged(cfg, nranks);
   if (cfg->flags & RHJ_FLAG_DEBUG_ENV) {
     // Ablation switches; only read when the caller asks for them.
-    if (const char *e = getenv("RHJ_SCATTER")) {
-      const int want = strcmp(e, "legacy") == 0 ? 0 : strcmp(e, "tiles") == 0 ? 2 : 3;
-      const size_t smem_limit = 227 * 1024;
-      const bool net_fits = (cfg->tuple_bytes == 16 ? scatter3_smem_bytes<InputSource<16>>(c->P)
-                                                    : scatter3_smem_bytes<InputSource<8>>(c->P)) <= smem_limit;
-      const bool loc_fits = !cfg->enable_two_level || scatter3_smem_bytes<ValueSource>(c->L) <= smem_limit;
-      if (want == 0 || (want == 2 && net_fits && loc_fits)) c->tune_scatter = want;
-    }
-    if (const char *e = getenv("RHJ_TPB")) c->tune_tpb = atoi(e) == 1024 ? 1024 : 512;
-    if (const char *e = getenv("RHJ_L2AHEAD")) c->tune_l2_ahead = c->tune_l2_ahead_net = std::max(0, std::min(32, atoi(e)));
-    if (const char *e = getenv("RHJ_HIST_REP")) c->tune_hist_rep = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("RHJ_SCATTER"))
+      if (strcmp(e, "legacy") == 0) c->tune_scatter = 0;
     if (const char *e = getenv("RHJ_BP")) c->tune_legacy_bp = strcmp(e, "legacy") == 0;
     if (const char *e = getenv("RHJ_BP_TPB")) c->tune_bp_tpb = atoi(e) == 512 ? 512 : 1024;
     if (const char *e = getenv("RHJ_PUSH_SMS")) c->tune_push_sms = std::max(0, std::min(64, atoi(e)));
@@ -372,7 +358,7 @@ static uint64_t default_window_cap(const rhj_config *cfg, uint64_t max_local) {
 }
 
 static void compute_layout(const rhj_config *cfg, int rank, int nranks, const uint64_t max_local[2],
-                           const uint64_t wcap_in[2], bool tiles, bool staged, Layout *lay) {
+                           const uint64_t wcap_in[2], bool staged, Layout *lay) {
   const uint32_t P = 1u << cfg->network_fanout_bits;
   const uint32_t L = cfg->enable_two_level ? (1u << cfg->local_fanout_bits) : 1u;
   const uint32_t nowned = owned_partitions(P, rank, nranks);
@@ -390,15 +376,6 @@ static void compute_layout(const rhj_config *cfg, int rank, int nranks, const ui
     if (cfg->flags & RHJ_FLAG_STAGE_HOST_INPUTS) add(max_local[k] * cfg->tuple_bytes);
     add((uint64_t)lay->max_chunks1[k] * P * 4);
     if (cfg->enable_two_level) add((uint64_t)lay->max_chunks2[k] * L * 4);
-    const uint64_t tpc = chunk / kTile;
-    if (tiles) {
-      add((uint64_t)lay->max_chunks1[k] * tpc * P * 4);
-      add((uint64_t)lay->max_chunks1[k] * tpc * P * 2);
-    }
-    if (tiles && cfg->enable_two_level) {
-      add((uint64_t)lay->max_chunks2[k] * tpc * L * 4);
-      add((uint64_t)lay->max_chunks2[k] * tpc * L * 2);
-    }
   }
   for (int i = 0; i < 6; ++i) add(2ull * P * 8);   // local, global, base, rel, abs, dest
   add((uint64_t)P * 4);                            // assignment
@@ -424,7 +401,7 @@ extern "C" uint64_t rhj_workspace_bytes(const rhj_config *cfg, int nranks, uint6
   if (!cfg || validate_config(cfg, 0, nranks)) return 0;
   Layout lay;
   uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
-  compute_layout(cfg, 0, nranks, ml, wc, false, exchange_is_staged(cfg, nranks), &lay);  // rank 0 owns the most partitions
+  compute_layout(cfg, 0, nranks, ml, wc, exchange_is_staged(cfg, nranks), &lay);  // rank 0 owns the most partitions
   return lay.total;
 }
 
@@ -443,8 +420,7 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
   RHJ_CUDA(cudaSetDevice(ctx->device));
   uint64_t ml[2] = {max_local_inner, max_local_outer}, wc[2] = {window_inner_cap, window_outer_cap};
   Layout lay;
-  const bool tiles = ctx->tune_scatter == 2;
-  compute_layout(&ctx->cfg, ctx->rank, ctx->nranks, ml, wc, tiles, ctx->staged_exchange, &lay);
+  compute_layout(&ctx->cfg, ctx->rank, ctx->nranks, ml, wc, ctx->staged_exchange, &lay);
   for (int k = 0; k < 2; ++k) {
     if (ml[k] >= (1ull << 32) || lay.window_cap[k] >= (1ull << 32))
       return fail(RHJ_ERR_INVALID, "relation %d: per-rank sizes must stay below 2^32 tuples", k);
@@ -473,11 +449,6 @@ extern "C" int rhj_plan(rhj_ctx *ctx, uint64_t max_local_inner, uint64_t max_loc
     }
     if (!rc) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * P, &ctx->chunk1_hist[k]);
     if (!rc && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * L, &ctx->chunk2_hist[k]);
-    const uint64_t tpc = ctx->tiles_per_chunk;
-    if (!rc && tiles) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_off[k]);
-    if (!rc && tiles) rc = carve(ctx, (uint64_t)lay.max_chunks1[k] * tpc * P, &ctx->tile1_start[k]);
-    if (!rc && tiles && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_off[k]);
-    if (!rc && tiles && ctx->cfg.enable_two_level) rc = carve(ctx, (uint64_t)lay.max_chunks2[k] * tpc * L, &ctx->tile2_start[k]);
   }
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_local_hist);
   if (!rc) rc = carve(ctx, 2ull * P, &ctx->d_global);
@@ -598,18 +569,8 @@ static int record(rhj_ctx *ctx, int which, cudaStream_t st) {
 
 template <class Source, class Map>
 static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                            uint32_t *chunk_hist, uint32_t *tile_off, uint16_t *tile_start, cudaStream_t st) {
+                            uint32_t *chunk_hist, cudaStream_t st) {
   if (grid_chunks == 0) return RHJ_OK;
-  if (ctx->tune_scatter == 2) {  // offset-driven scatter: per-tile metadata
-    // few replicas: every replica has to be summed per tile, and 256 random bins rarely collide
-    uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, (256u * ctx->tune_hist_rep) / nbins));
-    size_t smem = ((size_t)2 * nbins * nrep + nbins + 80) * 4;
-    uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)(ctx->sm_count - ctx->reserve_sms) * 4);
-    k_histogram_tiles<Source, Map><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, ctx->tiles_per_chunk, chunk_hist,
-                                                                  tile_off, tile_start, ctx->d_status);
-    RHJ_CHECK_LAUNCH("k_histogram_tiles");
-    return RHJ_OK;
-  }
   const bool agg = (ctx->cfg.flags & RHJ_FLAG_HIST_WARP_AGGREGATE) != 0;
   uint32_t nrep = std::max<uint32_t>(1, std::min<uint32_t>(kHistTPB / 32, 4096 / nbins));
   size_t smem = (size_t)nbins * nrep * 4;
@@ -619,24 +580,6 @@ static int launch_histogram(rhj_ctx *ctx, const Source &src, const Map &cm, uint
   else
     k_histogram<Source, Map, false><<<grid, kHistTPB, smem, st>>>(src, cm, nbins, nrep, chunk_hist, ctx->d_status);
   RHJ_CHECK_LAUNCH("k_histogram");
-  return RHJ_OK;
-}
-
-template <class Source, class Map, int TPB>
-static int launch_scatter3(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                           const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
-                           const uint64_t *bin_base, cudaStream_t st) {
-  size_t smem = scatter3_smem_bytes<Source>(nbins);
-  auto kern = k_scatter3<Source, Map, TPB>;
-  RHJ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  RHJ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem));
-  if (per_sm < 1) return fail(RHJ_ERR_INVALID, "scatter kernel does not fit (%zu bytes of shared memory at %u bins)", smem, nbins);
-  // reserve_sms: leave some SMs to a concurrently running push kernel (staged exchange)
-  uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)((ctx->sm_count - ctx->reserve_sms) * per_sm));
-  kern<<<grid, TPB, smem, st>>>(src, cm, nbins, ctx->tiles_per_chunk, chunk_off, tile_off, tile_start, bin_base,
-                                ctx->d_status, Source::kDigitFromValue ? ctx->tune_l2_ahead : ctx->tune_l2_ahead_net);
-  RHJ_CHECK_LAUNCH("k_scatter3");
   return RHJ_OK;
 }
 
@@ -709,16 +652,11 @@ static int launch_scatter_wc(rhj_ctx *ctx, const Source &src, const Map &cm, uin
 
 template <class Source, class Map>
 static int launch_scatter(rhj_ctx *ctx, const Source &src, const Map &cm, uint32_t grid_chunks, uint32_t nbins,
-                          const uint32_t *chunk_off, const uint32_t *tile_off, const uint16_t *tile_start,
-                          const uint64_t *bin_base, cudaStream_t st, uint32_t c_lo = 0, uint32_t c_hi = 0xFFFFFFFFu) {
+                          const uint32_t *chunk_off, const uint64_t *bin_base, cudaStream_t st, uint32_t c_lo = 0,
+                          uint32_t c_hi = 0xFFFFFFFFu) {
   if (grid_chunks == 0) return RHJ_OK;
   if (ctx->tune_scatter == 3)
     return launch_scatter_wc(ctx, src, cm, grid_chunks, nbins, chunk_off, bin_base, st, c_lo, c_hi);
-  if (ctx->tune_scatter == 2) {
-    if (ctx->tune_tpb == 1024)
-      return launch_scatter3<Source, Map, 1024>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
-    return launch_scatter3<Source, Map, 512>(ctx, src, cm, grid_chunks, nbins, chunk_off, tile_off, tile_start, bin_base, st);
-  }
   size_t smem = scatter_smem_bytes(nbins);
   RHJ_CUDA(cudaFuncSetAttribute(k_scatter<Source, Map>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   uint32_t grid = std::min<uint32_t>(grid_chunks, (uint32_t)ctx->sm_count * 2);
@@ -735,11 +673,7 @@ static int histogram_chunks(rhj_ctx *ctx, int k, uint32_t c_lo, uint32_t c_hi, c
   InputSource<TB> src{static_cast<const char *>(ctx->input[k]) + first * TB, ctx->P - 1, ctx->cfg.network_fanout_bits,
                       ctx->key_shift};
   ChunkMapFlat cm{std::min<uint64_t>(ctx->input_n[k] - first, (uint64_t)(c_hi - c_lo) * ctx->chunk1), ctx->chunk1, c_hi - c_lo};
-  const uint64_t row = (uint64_t)c_lo * ctx->P;
-  const uint64_t trow = row * ctx->tiles_per_chunk;
-  return launch_histogram(ctx, src, cm, c_hi - c_lo, ctx->P, ctx->chunk1_hist[k] + row,
-                          ctx->tile1_off[k] ? ctx->tile1_off[k] + trow : nullptr,
-                          ctx->tile1_start[k] ? ctx->tile1_start[k] + trow : nullptr, st);
+  return launch_histogram(ctx, src, cm, c_hi - c_lo, ctx->P, ctx->chunk1_hist[k] + (uint64_t)c_lo * ctx->P, st);
 }
 
 // per-chunk counts -> exclusive per-chunk offsets + the relation's local histogram
@@ -922,10 +856,10 @@ extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) 
     if (ctx->staged_exchange && (k == 1 || g > 0)) ctx->reserve_sms = std::max(saved_reserve, ctx->tune_push_sms);
     if (ctx->cfg.tuple_bytes == 16) {
       InputSource<16> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, nch, ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, c_lo, groups > 1 ? c_hi : 0xFFFFFFFFu);
+      rc = launch_scatter(ctx, src, cm, nch, ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st, c_lo, groups > 1 ? c_hi : 0xFFFFFFFFu);
     } else {
       InputSource<8> src{ctx->input[k], ctx->P - 1, ctx->cfg.network_fanout_bits, ctx->key_shift};
-      rc = launch_scatter(ctx, src, cm, nch, ctx->P, ctx->chunk1_hist[k], ctx->tile1_off[k], ctx->tile1_start[k], ctx->d_dest + (uint64_t)k * ctx->P, st, c_lo, groups > 1 ? c_hi : 0xFFFFFFFFu);
+      rc = launch_scatter(ctx, src, cm, nch, ctx->P, ctx->chunk1_hist[k], ctx->d_dest + (uint64_t)k * ctx->P, st, c_lo, groups > 1 ? c_hi : 0xFFFFFFFFu);
     }
     if (rc) break;
     if (ctx->staged_exchange) {
@@ -1073,8 +1007,7 @@ extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
     ValueSource src{ctx->window[k], ctx->key_shift, L - 1};
     ChunkMapSeg cm{ctx->d_part_off + (uint64_t)k * ctx->nowned, ctx->d_part_cnt + (uint64_t)k * ctx->nowned,
                    ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), ctx->nowned, ctx->chunk2};
-    rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
-                          ctx->tile2_start[k], st);
+    rc = launch_histogram(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], st);
     if (rc) return rc;
     dim3 grid((L + 31) / 32, ctx->nowned);
     k_colscan<8><<<grid, 8 * 32, 0, st>>>(ctx->chunk2_hist[k], L, ctx->d_cstart + (uint64_t)k * (ctx->nowned + 1), 0,
@@ -1082,8 +1015,8 @@ extern "C" int rhj_local_partition_rel(rhj_ctx *ctx, int which, void *stream) {
     RHJ_CHECK_LAUNCH("k_colscan(local)");
     rc = launch_plan_local(ctx, k, k + 1, other_done, st);
     if (rc) return rc;
-    rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k], ctx->tile2_off[k],
-                        ctx->tile2_start[k], ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
+    rc = launch_scatter(ctx, src, cm, ctx->max_chunks2[k], L, ctx->chunk2_hist[k],
+                        ctx->d_sub_addr + (uint64_t)k * ctx->NS, st);
     ctx->reserve_sms = saved_reserve;
     if (rc) return rc;
   }
@@ -1248,9 +1181,14 @@ extern "C" int rhj_get_write_offsets(rhj_ctx *ctx, int which, uint64_t *out_host
 static int owned_slot(rhj_ctx *ctx, uint32_t p, uint32_t *j) {
   if (p >= ctx->P) return fail(RHJ_ERR_INVALID, "partition %u outside [0,%u)", p, ctx->P);
   uint32_t owner = 0;
-  int rc = copy_out(ctx, &owner, ctx->d_assign + p, 4, nullptr);
-  if (!rc) rc = copy_out(ctx, j, ctx->d_slot_of + p, 4, nullptr);
-  if (rc) return rc;
+  if (!(ctx->cfg.flags & RHJ_FLAG_BALANCED_ASSIGNMENT) || ctx->nranks == 1) {
+    owner = p % (uint32_t)ctx->nranks;  // AssignmentMap.cpp:41-43: known without asking the device
+    *j = p / (uint32_t)ctx->nranks;
+  } else {
+    int rc = copy_out(ctx, &owner, ctx->d_assign + p, 4, nullptr);
+    if (!rc) rc = copy_out(ctx, j, ctx->d_slot_of + p, 4, nullptr);
+    if (rc) return rc;
+  }
   if (owner != (uint32_t)ctx->rank) return fail(RHJ_ERR_INVALID, "partition %u not owned by rank %d", p, ctx->rank);
   return RHJ_OK;
 }

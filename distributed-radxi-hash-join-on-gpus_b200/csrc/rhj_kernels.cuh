@@ -1,21 +1,20 @@
 // rhj_kernels.cuh -- the four join stages as sm_100a kernels.
 //
-//   K1  k_histogram_tiles  histograms/LocalHistogram.cpp:35-53 (and LocalPartitioning.cpp:138-163);
-//                          also writes, per 8192-tuple tile, each tuple's rank inside its bin
-//                          and the bins' start slots, so the scatter needs no counting pass
+//   K1  k_histogram        histograms/LocalHistogram.cpp:35-53 (and LocalPartitioning.cpp:138-163), per chunk
 //   Ks  k_colscan          per-chunk exclusive offsets (what lets the scatter write exact,
 //                          write-once positions; OffsetMap.cpp:75-85 does this per rank only)
 //   Kp  k_plan_network     GlobalHistogram.cpp:31-48, AssignmentMap.cpp:34-49, OffsetMap.cpp:59-93
-//   K2/K3 k_scatter3       NetworkPartitioning.cpp:116-173 / LocalPartitioning.cpp:194-250
-//   Kx  k_push             the staged exchange: contiguous per-destination runs -> peer windows
-//                          (data/Window.cpp:108-115, MPI_Put)
+//   K2/K3 k_scatter_wc     NetworkPartitioning.cpp:116-173 / LocalPartitioning.cpp:194-250: write-combining
+//                          rings in shared memory, only whole 128-byte lines leave the SM
+//   Kx  k_push             the staged exchange (three and more ranks): contiguous per-destination runs ->
+//                          peer windows (data/Window.cpp:108-115, MPI_Put); k_signal_peers / k_wait_peers:
+//                          the barrier of operators/HashJoin.cpp:119-121 as arrival flags
 //   Kq  k_plan_local/items LocalPartitioning.cpp:165-192 (8-tuple padded prefix) + work list
 //   K4  k_build_probe3     BuildProbe.cpp:47-121
-//   k_histogram, k_scatter, k_build_probe are the first-generation kernels.  They run fan-outs of
-//   more than 2048 bins per pass (the offset-driven pair's shared-memory arrays stop fitting),
-//   single-pass mode and work items beyond the expanded list (k_build_probe), the allocation-free
-//   histogram entry point (k_histogram), and stay selectable as the ablation baseline
-//   (RHJ_SCATTER=legacy, RHJ_BP=legacy).
+//   k_scatter and k_build_probe are the first-generation kernels.  They run fan-outs of more than 1024
+//   bins per pass (the rings stop fitting shared memory), single-pass mode and work items beyond the
+//   expanded list (k_build_probe), and stay selectable as the ablation baseline (RHJ_SCATTER=legacy,
+//   RHJ_BP=legacy with RHJ_FLAG_DEBUG_ENV).
 //
 // All stages are HBM-bound integer work (no tensor cores).  Work is cut into
 // fixed-size chunks of consecutive tuples; the histogram and the scatter of a pass
@@ -34,10 +33,8 @@ constexpr int kHistUnroll = 8;
 constexpr int kScatTPB = 512;
 constexpr int kScatIPT = 8;
 constexpr int kScatTile = kScatTPB * kScatIPT;  // tuples staged in shared memory per tile
-constexpr int kTile = 8192;                      // tuples per tile of the offset-driven kernels
-constexpr int kTileUnroll = kTile / kHistTPB;
+constexpr int kChunkGranule = 8192;              // chunk_tuples must be a multiple of this
 constexpr uint32_t kInvalidDigit = 0xFFFFFFFFu;
-constexpr int kScatL2Ahead = 3;  // tiles between the register prefetch and the L2 prefetch
 
 enum DevStatus : int {
   kDevOk = 0,
@@ -178,259 +175,6 @@ __global__ void __launch_bounds__(kHistTPB) k_histogram(Source src, Map cm, uint
       chunk_hist[(uint64_t)c * nbins + i] = s;
     }
     __syncthreads();
-  }
-}
-
-// ---------------------------------------------------------------------------------
-// K1t: histogram with tile granularity.  The histogram kernels have instruction and
-// shared-memory slack (they only read), the scatter kernels have none; so everything
-// the scatter would otherwise have to derive per tile is computed here, once:
-//   chunk_hist [chunk][nbins] u32   counts per chunk (as k_histogram)
-//   tile_off   [row][nbins]   u32   tuples of the bin in EARLIER tiles of the same chunk
-//   tile_start [row][nbins]   u16   exclusive prefix over the bins inside the tile
-//                                   (= where the bin's run starts in the sorted tile)
-// row = chunk * tiles_per_chunk + tile; a tile is kTile tuples.
-// ---------------------------------------------------------------------------------
-static_assert(kHistTPB * kTileUnroll == kTile, "histogram tile must equal the scatter tile");
-
-template <class Source, class Map>
-__global__ void __launch_bounds__(kHistTPB, 4) k_histogram_tiles(Source src, Map cm, uint32_t nbins, uint32_t nrep,
-                                                               uint32_t tiles_per_chunk,
-                                                               uint32_t *__restrict__ chunk_hist,
-                                                               uint32_t *__restrict__ tile_off,
-                                                               uint16_t *__restrict__ tile_start,
-                                                               const int *__restrict__ status) {
-  extern __shared__ uint32_t sh_hist[];  // [2][nrep][nbins] counters | [nbins] running | tmp[2][33]
-  if (*status != kDevOk) return;
-  uint32_t *running = sh_hist + 2 * nrep * nbins;
-  uint32_t *tmp = running + nbins;
-  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t nchunks = cm.count();
-  const bool fast = nbins <= kHistTPB;  // one bin per thread: two barriers per tile, counters double-buffered
-  for (uint32_t i = tid; i < 2 * nbins * nrep; i += kHistTPB) sh_hist[i] = 0;
-  uint32_t par = 0;
-  for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
-    for (uint32_t i = tid; i < nbins; i += kHistTPB) running[i] = 0;
-    __syncthreads();
-    uint64_t b, e;
-    uint32_t seg;
-    cm.range(c, b, e, seg);
-    uint64_t row = (uint64_t)c * tiles_per_chunk;
-    for (uint64_t base = b; base < e; base += kTile, ++row, par ^= 1) {
-      uint32_t *set = sh_hist + par * nrep * nbins;
-      uint32_t *my = set + (warp % nrep) * nbins;
-      uint32_t dg[kTileUnroll];
-#pragma unroll
-      for (int u = 0; u < kTileUnroll; ++u) {
-        uint64_t i = base + (uint64_t)u * kHistTPB + tid;
-        dg[u] = i < e ? src.digit(i) : kInvalidDigit;
-      }
-#pragma unroll
-      for (int u = 0; u < kTileUnroll; ++u)
-        if (dg[u] != kInvalidDigit) atomicAdd(&my[dg[u]], 1u);
-      __syncthreads();
-      if (fast) {
-        uint32_t cnt = 0;
-        if (tid < nbins) {
-          for (uint32_t r = 0; r < nrep; ++r) {
-            cnt += set[r * nbins + tid];
-            set[r * nbins + tid] = 0;
-          }
-        }
-        const uint32_t incl = warp_inclusive_scan(cnt);
-        uint32_t *wt = tmp + par * 33;
-        if (lane == 31) wt[warp] = incl;
-        __syncthreads();
-        if (tid < nbins) {
-          uint32_t before = 0;
-          for (uint32_t w = 0; w < warp; ++w) before += wt[w];
-          const uint32_t run = running[tid];
-          tile_off[row * nbins + tid] = run;
-          tile_start[row * nbins + tid] = (uint16_t)(before + incl - cnt);
-          running[tid] = run + cnt;
-        }
-      } else {
-        uint32_t carry = 0;
-        for (uint32_t d0 = 0; d0 < nbins; d0 += kHistTPB) {
-          const uint32_t d = d0 + tid;
-          uint32_t cnt = 0;
-          if (d < nbins) {
-            for (uint32_t r = 0; r < nrep; ++r) {
-              cnt += set[r * nbins + d];
-              set[r * nbins + d] = 0;
-            }
-          }
-          uint32_t total;
-          const uint32_t ex = block_exclusive_scan<uint32_t>(cnt, tmp, &total);
-          if (d < nbins) {
-            const uint32_t run = running[d];
-            tile_off[row * nbins + d] = run;
-            tile_start[row * nbins + d] = (uint16_t)(carry + ex);
-            running[d] = run + cnt;
-          }
-          carry += total;
-        }
-      }
-    }
-    __syncthreads();
-    for (uint32_t i = tid; i < nbins; i += kHistTPB) chunk_hist[(uint64_t)c * nbins + i] = running[i];
-    __syncthreads();
-  }
-}
-// ---------------------------------------------------------------------------------
-// K2 / K3, offset-driven: every (tile, bin) destination and every bin's position inside
-// the sorted tile is known before the kernel starts (k_histogram_tiles + k_colscan), so a
-// tile needs no counting and no scan here: one shared atomic per tuple hands out its slot
-// in the staging buffer, and ONE barrier per tile separates "place tile t+1" from
-// "write tile t+1".  Inside a chunk the loop is software-pipelined over tiles:
-//     iteration t:  write tile t (staged last iteration) | place tile t+1 (loaded last
-//     iteration) | load tile t+2 into registers | prepare the per-bin slots of tile t+2
-//     | ask L2 for tile t+2+ahead | barrier
-// Staging buffers alternate (2), the per-bin slot/address arrays rotate (3), so nothing
-// read in an iteration is written in the same one.  Everything is addressed relative to
-// the chunk (32-bit indices, row pointers advanced by nbins per tile) to keep the hot
-// loop short: the kernel is bound by instruction issue and shared-memory wavefronts as
-// much as by HBM.
-// ---------------------------------------------------------------------------------
-template <class Source>
-__host__ __device__ inline size_t scatter3_smem_bytes(uint32_t nbins) {
-  return 2 * (size_t)kTile * 8 + (Source::kDigitFromValue ? 0 : 2 * (size_t)kTile * 2) +
-         3 * (size_t)nbins * (8 + 4) + 64;
-}
-
-template <class Source, class Map, int TPB>
-__global__ void __launch_bounds__(TPB, TPB <= 512 ? 2 : 1)
-    k_scatter3(const Source src, const Map cm, const uint32_t nbins, const uint32_t tiles_per_chunk,
-               const uint32_t *__restrict__ chunk_off, const uint32_t *__restrict__ tile_off,
-               const uint16_t *__restrict__ tile_start, const uint64_t *__restrict__ bin_base,
-               const int *__restrict__ status, const int l2_ahead) {
-  using Raw = typename Source::Raw;
-  constexpr int IPT = kTile / TPB;
-  constexpr uint32_t T = kTile;
-  extern __shared__ __align__(128) unsigned char sh_raw[];
-  if (*status != kDevOk) return;
-  uint64_t *const stage = reinterpret_cast<uint64_t *>(sh_raw);           // [2][T]
-  uint64_t *const delta = stage + 2 * T;                                  // [3][nbins]
-  uint32_t *const pos = reinterpret_cast<uint32_t *>(delta + 3 * nbins);  // [3][nbins]
-  uint16_t *const dig = reinterpret_cast<uint16_t *>(pos + 3 * nbins);    // [2][T]  (pass 1 only)
-  const uint32_t tid = threadIdx.x;
-  const uint32_t nchunks = cm.count();
-  const bool one_bin_per_thread = nbins <= (uint32_t)TPB;
-
-  for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
-    uint64_t cb, ce;
-    uint32_t seg;
-    cm.range(c, cb, ce, seg);
-    const uint32_t count = (uint32_t)(ce - cb);
-    const uint32_t ntiles = (count + T - 1) / T;
-    const Raw *const in = static_cast<const Raw *>(src.base()) + cb;
-    const uint32_t *const toff = tile_off + (size_t)c * tiles_per_chunk * nbins;
-    const uint16_t *const tst = tile_start + (size_t)c * tiles_per_chunk * nbins;
-    const uint32_t *const coff = chunk_off + (size_t)c * nbins;
-    const uint64_t *const bb = bin_base + (size_t)seg * nbins;
-    // destination of this chunk's first tuple of bin `tid`
-    uint64_t cbase = 0;
-    if (one_bin_per_thread && tid < nbins) cbase = bb[tid] + (uint64_t)coff[tid] * 8;
-
-    // per-bin slot counter and destination for tile t, into slot-array set `buf`
-    auto small_init = [&](uint32_t t, uint32_t buf) {
-      for (uint32_t d = tid; d < nbins; d += TPB) {
-        const uint32_t lst = tst[(size_t)t * nbins + d];
-        const uint32_t off = toff[(size_t)t * nbins + d];
-        pos[buf * nbins + d] = lst;
-        delta[buf * nbins + d] = bb[d] + ((uint64_t)coff[d] + off - lst) * 8;
-      }
-    };
-    auto load_raw = [&](uint32_t t, Raw (&raw)[IPT]) {
-      const uint32_t n = count - t * T;
-      const Raw *p = in + t * T + tid;
-      if (n >= T) {
-#pragma unroll
-        for (int u = 0; u < IPT; ++u) raw[u] = ld_stream(p + u * TPB);
-      } else {
-#pragma unroll
-        for (int u = 0; u < IPT; ++u)
-          if (u * TPB + tid < n) raw[u] = ld_stream(p + u * TPB);
-      }
-    };
-    auto place = [&](uint32_t t, const Raw (&raw)[IPT], uint32_t sb, uint32_t buf) {
-      const uint32_t n = count - t * T;
-      uint64_t *st = stage + sb * T;
-      uint16_t *dg_out = dig + sb * T;
-      uint32_t *ps = pos + buf * nbins;
-#pragma unroll
-      for (int u = 0; u < IPT; ++u) {
-        if (n >= T || u * TPB + tid < n) {
-          uint64_t v;
-          uint32_t d;
-          src.decode(raw[u], v, d);
-          const uint32_t p = atomicAdd(&ps[d], 1u);
-          st[p] = v;
-          if (!Source::kDigitFromValue) dg_out[p] = (uint16_t)d;
-        }
-      }
-    };
-    auto write_out = [&](uint32_t t, uint32_t sb, uint32_t buf) {
-      const uint32_t n = count - t * T;
-      const uint64_t *st = stage + sb * T + tid;
-      const uint16_t *dg_in = dig + sb * T + tid;
-      const uint64_t *dl = delta + buf * nbins;
-      const uint32_t byte0 = tid * 8;
-#pragma unroll
-      for (int u = 0; u < IPT; ++u) {
-        if (n >= T || u * TPB + tid < n) {
-          const uint64_t v = st[u * TPB];
-          const uint32_t d = Source::kDigitFromValue ? src.digit_of_value(v) : (uint32_t)dg_in[u * TPB];
-          st_stream_u64(reinterpret_cast<uint64_t *>(dl[d] + (byte0 + u * TPB * 8)), v);
-        }
-      }
-    };
-
-    Raw raw[IPT];
-    small_init(0, 0);
-    load_raw(0, raw);
-    __syncthreads();
-    place(0, raw, 0, 0);
-    if (ntiles > 1) {
-      small_init(1, 1);
-      load_raw(1, raw);
-    }
-    if (tid == 0)
-      for (int a = 2; a < 2 + l2_ahead && (uint32_t)a < ntiles; ++a)
-        prefetch_l2_range(in + (size_t)a * T, (uint64_t)min(T, count - a * T) * sizeof(Raw));
-    __syncthreads();
-
-    uint32_t sb = 0, buf = 0;
-    for (uint32_t t = 0; t < ntiles; ++t) {
-      const uint32_t buf1 = buf == 2 ? 0 : buf + 1, buf2 = buf1 == 2 ? 0 : buf1 + 1;
-      const bool have2 = t + 2 < ntiles;
-      // slots of tile t+2: loads now, stores after the work below
-      uint32_t lst = 0, off = 0;
-      if (have2 && one_bin_per_thread && tid < nbins) {
-        lst = tst[(size_t)(t + 2) * nbins + tid];
-        off = toff[(size_t)(t + 2) * nbins + tid];
-      }
-      if (tid == 0 && l2_ahead > 0 && t + 2 + l2_ahead < ntiles) {
-        const uint32_t a = t + 2 + l2_ahead;
-        prefetch_l2_range(in + (size_t)a * T, (uint64_t)min(T, count - a * T) * sizeof(Raw));
-      }
-      write_out(t, sb, buf);
-      if (t + 1 < ntiles) place(t + 1, raw, sb ^ 1, buf1);
-      if (have2) {
-        if (one_bin_per_thread) {
-          if (tid < nbins) {
-            pos[buf2 * nbins + tid] = lst;
-            delta[buf2 * nbins + tid] = cbase + ((uint64_t)off - lst) * 8;
-          }
-        } else {
-          small_init(t + 2, buf2);
-        }
-        load_raw(t + 2, raw);
-      }
-      __syncthreads();
-      sb ^= 1;
-      buf = buf1;
-    }
   }
 }
 
