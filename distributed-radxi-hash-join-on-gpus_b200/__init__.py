@@ -412,4 +412,4 @@ def apply_perm(tensor, n: int, stride_words: int, domain: int, seed: int):
     check(lib().rhj_apply_perm(_ptr(tensor), n, stride_words, domain, seed, _stream()))
 
 
-from .hashjoin import HashJoin, Relation, join_multi_rank  # noqa: E402,F401
+from .hashjoin import HashJoin, Relation, distribute, join_multi_rank  # noqa: E402,F401

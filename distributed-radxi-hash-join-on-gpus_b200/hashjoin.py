@@ -126,6 +126,79 @@ def _host_barrier_group(group=None):
     return _HOST_GROUPS[key]
 
 
+def _splitmix64(x: int) -> int:
+    m = (1 << 64) - 1
+    x = (x + 0x9E3779B97F4A7C15) & m
+    x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & m
+    x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & m
+    return x ^ (x >> 31)
+
+
+def perm_positions(n: int, seed: int, device):
+    """perm(i) for i in [0, n): the generator's bijection (rhj_fill_perm / oracle orc_perm) evaluated
+    with torch integer ops, so that it runs wherever the relation lives (cuda, or cpu under gloo)."""
+    import torch
+    x = torch.arange(n, dtype=torch.int64, device=device)
+    if n <= 1:
+        return torch.zeros_like(x)
+    b = max(1, (n - 1).bit_length())
+    mask, sh = (1 << b) - 1, max(1, b // 2)
+    s64 = lambda v: v - (1 << 64) if v >= (1 << 63) else v  # two's complement: int64 products wrap like u64
+    ma = [(s64(_splitmix64(seed + 2 * i) | 1), s64(_splitmix64(seed + 2 * i + 1))) for i in range(3)]
+
+    def rounds(v):
+        for m_, a_ in ma:
+            v = (v * m_ + a_) & mask
+            v = v ^ (v >> sh)
+        return v
+
+    x = rounds(x)
+    while True:  # cycle walking: values that left [0, n) go round again
+        out = x >= n
+        if not bool(out.any()):
+            return x
+        x = torch.where(out, rounds(x), x)
+
+
+def distribute(rel: Relation, nranks: int, rank: int, seed: int, group=None) -> None:
+    """Relation::distribute (data/Relation.cpp:99-141) on the device, in place, for relations of the
+    harness's counter-based generator: this rank swaps section (rank + i) % n with
+    rank i -- tuples cross NVLink through point-to-point NCCL transfers, no host copy of the relation
+    exists -- and then permutes its keys over the positions with the generator's bijection where the
+    reference shuffles them with rand() (keys move, rids stay, data/Relation.cpp:87-97).  Every rank
+    calls it (collective); all ranks hold the same number of 16-byte tuples.  Bit-identical to
+    oracle.distribute_perm (orc_distribute_perm)."""
+    import torch
+    import torch.distributed as dist
+    if rel.tuple_bytes != 16:
+        raise ValueError("distribute works on 16-byte {key, rid} tuples")
+    n = rel.local_size
+    t = rel.data[:2 * n].view(n, 2)
+    if nranks > 1:
+        sec = n // nranks
+        last = n - (nranks - 1) * sec
+        ops, bufs = [], []
+        for i in range(nranks):
+            if i == rank:
+                continue
+            s_ = (rank + i) % nranks
+            lo, size = s_ * sec, (last if s_ == nranks - 1 else sec)
+            if size == 0:
+                continue
+            send = t[lo:lo + size].contiguous()
+            recv = torch.empty_like(send)
+            peer = i if group is None else dist.get_global_rank(group, i)
+            ops.append(dist.P2POp(dist.isend, send, peer, group))
+            ops.append(dist.P2POp(dist.irecv, recv, peer, group))
+            bufs.append((lo, size, recv, send))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        for lo, size, recv, _ in bufs:
+            t[lo:lo + size] = recv
+    t[:, 0] = t[perm_positions(n, seed + rank, t.device), 0]
+
+
 _SIDE_STREAMS = {}
 
 

@@ -74,6 +74,36 @@ void orc_fill_modulo(orc_rng *rng, orc_tuple *t, uint64_t n, uint64_t start_key,
 /* data/Relation.cpp:99-141.  Rank `me` and rank `i` swap their sections numbered
  * (me+i) % n (both sides compute the same section index), section (2*me)%n stays;
  * afterwards every rank reshuffles its keys (:139). Whole tuples (key AND rid) move. */
+/* Relation::distribute (data/Relation.cpp:99-141) for the harness's counter-based generator: the same
+ * pairwise section swaps (rank a and rank b exchange section (a + b) % n), then -- where the reference
+ * shuffles the key field with rand() (randomOrder, :87-97: keys move, rids stay) -- the keys of rank r
+ * are permuted by the generator's bijection over positions: key'[i] = key[orc_perm(i, local_size, seed + r)].
+ * The device-side distribute of the launchers must reproduce this bit for bit. */
+int orc_distribute_perm(orc_tuple **rels, uint64_t local_size, uint32_t nranks, uint64_t seed) {
+  uint64_t sec = local_size / nranks;
+  uint64_t last = local_size - (uint64_t)(nranks - 1) * sec;
+  orc_tuple *tmp = (orc_tuple *)malloc((last ? last : 1) * sizeof(orc_tuple));
+  uint64_t *keys = (uint64_t *)malloc((local_size ? local_size : 1) * sizeof(uint64_t));
+  if (!tmp || !keys) { free(tmp); free(keys); return -1; }
+  for (uint32_t a = 0; a < nranks; ++a) {
+    for (uint32_t b = a + 1; b < nranks; ++b) {
+      uint32_t section = (a + b) % nranks;
+      uint64_t start = (uint64_t)section * sec;
+      uint64_t size = (section == nranks - 1) ? last : sec;
+      memcpy(tmp, rels[a] + start, size * sizeof(orc_tuple));
+      memcpy(rels[a] + start, rels[b] + start, size * sizeof(orc_tuple));
+      memcpy(rels[b] + start, tmp, size * sizeof(orc_tuple));
+    }
+  }
+  for (uint32_t r = 0; r < nranks; ++r) {
+    for (uint64_t i = 0; i < local_size; ++i) keys[i] = rels[r][i].key;
+    for (uint64_t i = 0; i < local_size; ++i) rels[r][i].key = keys[orc_perm(i, local_size, seed + r)];
+  }
+  free(tmp);
+  free(keys);
+  return 0;
+}
+
 int orc_distribute(orc_rng **rngs, orc_tuple **rels, uint64_t local_size, uint32_t nranks) {
   uint64_t sec = local_size / nranks;
   uint64_t last = local_size - (uint64_t)(nranks - 1) * sec;

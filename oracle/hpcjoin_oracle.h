@@ -64,6 +64,8 @@ void orc_fill_modulo(orc_rng *rng, orc_tuple *t, uint64_t n, uint64_t start_key,
 void orc_random_order(orc_rng *rng, orc_tuple *t, uint64_t n);
 /* Relation::distribute for all ranks at once (equal local sizes). */
 int orc_distribute(orc_rng **rngs, orc_tuple **rels, uint64_t local_size, uint32_t nranks);
+/* the same for the harness generator: section swaps, then key'[i] = key[orc_perm(i, local_size, seed + rank)] */
+int orc_distribute_perm(orc_tuple **rels, uint64_t local_size, uint32_t nranks, uint64_t seed);
 
 /* Harness-owned counter-based generator for sizes where rand() Fisher-Yates
  * is too slow (SURVEY.md §7 hard part 6): key = perm_seed(first+i) over

@@ -72,6 +72,8 @@ def lib():
         L.orc_fill_modulo.argtypes = [vp, vp, u64, u64, u64, u64]
         L.orc_random_order.argtypes = [vp, vp, u64]
         L.orc_distribute.argtypes = [vp, vp, u64, u32]
+        L.orc_distribute_perm.argtypes = [vp, u64, u32, u64]
+        L.orc_distribute_perm.restype = C.c_int
         L.orc_perm.restype = u64
         L.orc_perm.argtypes = [u64, u64, u64]
         L.orc_fill_perm.argtypes = [vp, u64, u64, u64, u64, u64, u64, u64]
@@ -158,6 +160,14 @@ def fill_perm(n: int, first: int, domain: int, seed: int, modulo: int = 0, start
     t = np.zeros(n, TUPLE)
     lib().orc_fill_perm(_p(t), n, first, domain, seed, modulo, start_key, start_rid)
     return t
+
+
+def distribute_perm(rels: list, seed: int) -> None:
+    """In place: Relation::distribute for the harness generator (orc_distribute_perm)."""
+    n = len(rels[0])
+    assert all(len(r) == n for r in rels)
+    ps = (C.c_void_p * len(rels))(*[a.ctypes.data for a in rels])
+    assert lib().orc_distribute_perm(ps, n, len(rels), seed) == 0
 
 
 def fill_zipf(n: int, first: int, domain: int, theta: float, seed: int, start_rid: int = 0) -> np.ndarray:

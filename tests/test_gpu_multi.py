@@ -200,3 +200,37 @@ def test_baseline_configs_4_and_5_full_size_all_gpus(tmp_path, shape):
         json.dump(res, open(os.path.join(keep, f"config_{shape}_n{world}.json"), "w"))
     assert len(res["want"]) == 5 and None not in res["want"]
     assert res["got"] == res["want"]
+
+
+def _worker_distribute(rank, world, port, per, seed, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    t = torch.empty(2 * per, dtype=torch.int64, device=dev)
+    rhj.fill_perm(t, 16, per, rank * per, world * per, seed=11, start_rid=rank * per)  # generated on the device
+    rhj.distribute(rhj.Relation(t, per, world * per), world, rank, seed)               # exchanged over NVLink
+    torch.cuda.synchronize()
+    np.save(os.path.join(out_dir, f"dist{rank}.npy"), t.cpu().numpy().view(np.uint64).reshape(-1, 2))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_device_distribute_two_gpus(oracle, tmp_path):
+    """SURVEY.md 8(f2): generator + Relation::distribute without a host copy of the relation, equal to
+    orc_distribute_perm bit for bit (the same launcher code is checked over gloo in test_multirank_cpu.py)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    world, per, seed = 2, 1000003, 77
+    mp.spawn(_worker_distribute, args=(world, _free_port(), per, seed, str(tmp_path)), nprocs=world, join=True)
+    rels = [oracle.fill_perm(per, r * per, world * per, seed=11, start_rid=r * per) for r in range(world)]
+    oracle.distribute_perm(rels, seed)
+    for r in range(world):
+        assert np.array_equal(np.load(tmp_path / f"dist{r}.npy"), rels[r].view(np.uint64).reshape(-1, 2))

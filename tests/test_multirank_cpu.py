@@ -84,3 +84,49 @@ def test_two_ranks_gloo_offsets(oracle, tmp_path, knobs):
             assert np.array_equal(z[name + "_abs"], pl.abs_[r])
             assert np.array_equal(z[name + "_ws"], pl.window_size)
             assert int(z["total"][0]) == world * per
+
+
+def _worker_distribute(rank, world, port, per, seed, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # main.cpp:94-98 with the harness generator: rank r fills its own key range, then distribute()
+    mine = O.fill_perm(per, rank * per, world * per, seed=11, start_rid=rank * per)
+    t = torch.from_numpy(mine.view(np.int64).copy())
+    rel = rhj.Relation(t, per, world * per)
+    rhj.distribute(rel, world, rank, seed, None)
+    np.save(os.path.join(out_dir, f"dist{rank}.npy"), t.numpy().view(np.uint64).reshape(-1, 2))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,per", [(2, 10001), (3, 7000), (4, 4099)])
+def test_device_agnostic_distribute_equals_oracle(oracle, tmp_path, world, per):
+    """The launchers' Relation::distribute (torch point-to-point exchange + position bijection; the same code
+    runs on NCCL with device tensors) against orc_distribute_perm, bit for bit, ragged last section included."""
+    import torch.multiprocessing as mp
+    seed = 77
+    mp.spawn(_worker_distribute, args=(world, _free_port(), per, seed, str(tmp_path)), nprocs=world, join=True)
+    rels = [oracle.fill_perm(per, r * per, world * per, seed=11, start_rid=r * per) for r in range(world)]
+    before = np.sort(np.concatenate(rels).view(np.uint64).reshape(-1, 2)[:, 0])
+    oracle.distribute_perm(rels, seed)
+    for r in range(world):
+        got = np.load(tmp_path / f"dist{r}.npy")
+        assert np.array_equal(got, rels[r].view(np.uint64).reshape(-1, 2)), f"rank {r}"
+    after = np.sort(np.concatenate([np.load(tmp_path / f"dist{r}.npy")[:, 0] for r in range(world)]))
+    assert np.array_equal(before, after)  # a redistribution: the global key multiset is unchanged
+
+
+def test_perm_positions_equals_oracle(oracle):
+    import torch
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    for n, seed in ((1, 3), (2, 5), (1000, 7), (65537, 99), (100000, 123456789)):
+        got = rhj.hashjoin.perm_positions(n, seed, "cpu").numpy()
+        want = np.array([oracle.lib().orc_perm(i, n, seed) for i in range(n)], np.int64)
+        assert np.array_equal(got, want), (n, seed)
+        assert np.array_equal(np.sort(got), np.arange(n))
