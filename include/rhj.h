@@ -310,6 +310,12 @@ int rhj_apply_perm(uint64_t *vals_dev, uint64_t n, uint32_t stride_words, uint64
  *  - runs on the calling thread's current device, on `stream`.
  *  - the first call on each device looks up the array's device address; make that call
  *    before starting any stream capture.
+ *  - the array is part of the library's device code.  The CUDA runtime loads that code onto a
+ *    device the first time the device uses this library (lazy module loading, the default since
+ *    CUDA 12), and that load is the one moment this entry point does need free device memory:
+ *    4 MiB for the array plus the kernels' code.  An engine that is about to take all of the
+ *    GPU's memory should therefore make one call per device first (n = 0 is enough and launches
+ *    almost nothing), or run with CUDA_MODULE_LOADING=EAGER; after that no call allocates.
  *  - all calls on a device share the array: calls whose GPU work can overlap (different
  *    streams or host threads) race with each other; order them on one stream or
  *    synchronise between them.  The array keeps the previous call's contents; the
