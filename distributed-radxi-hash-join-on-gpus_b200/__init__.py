@@ -118,6 +118,7 @@ SYMBOLS = {
     "rhj_get_local_partition": (_int, [_vp, _int, _u32, _vp, _vp, _vp]),
     "rhj_get_partition_dev": (_int, [_vp, _int, _u32, _int, C.POINTER(_vp), C.POINTER(_u64)]),
     "rhj_build_probe": (_int, [_vp, _vp]),
+    "rhj_build_probe_accumulate": (_int, [_vp, _vp]),
     "rhj_build_probe_pairs": (_int, [_vp, _vp, _u64, _vp]),
     "rhj_get_result": (_int, [_vp, _resp, _vp]),
     "rhj_get_timings": (_int, [_vp, C.POINTER(Timings)]),
@@ -298,6 +299,9 @@ class Context:
     def build_probe(self):
         check(lib().rhj_build_probe(self.h, _stream()))
 
+    def build_probe_accumulate(self):
+        check(lib().rhj_build_probe_accumulate(self.h, _stream()))
+
     def build_probe_pairs(self, pairs, capacity: int | None = None):
         """Build/probe with materialised output: `pairs` is a device int64 tensor with room for
         2 * capacity values, filled with (rid_R, rid_S) rows in unspecified order."""
@@ -412,4 +416,4 @@ def apply_perm(tensor, n: int, stride_words: int, domain: int, seed: int):
     check(lib().rhj_apply_perm(_ptr(tensor), n, stride_words, domain, seed, _stream()))
 
 
-from .hashjoin import HashJoin, Relation, distribute, join_multi_rank  # noqa: E402,F401
+from .hashjoin import HashJoin, Relation, distribute, host_pieces, join_multi_rank, join_probe_pieces  # noqa: E402,F401

@@ -111,7 +111,8 @@ struct rhj_ctx {
   // peers (data/Window.cpp: target of MPI_Put)
   uint32_t *d_flags = nullptr;           // [2][64] arrival flags written by the peers
   uint64_t peer_flags[kMaxRanks] = {};   // the peers' flag arrays (0: none, e.g. ranks emulated on one device)
-  uint32_t epoch = 0;                    // joins started on this context; the value the flags carry
+  uint32_t epoch = 0;                    // joins started on this context
+  uint32_t epoch_rel[2] = {0, 0};        // network passes started per relation; the value that relation's flags carry
   bool use_flags = false;
   uint64_t peer_window[2][kMaxRanks] = {};
   void *ipc_base[kMaxRanks] = {};
@@ -691,6 +692,7 @@ static int histogram_scan(rhj_ctx *ctx, int k, cudaStream_t st) {
 static int begin_join(rhj_ctx *ctx, cudaStream_t st) {
   ctx->local_planned = false;
   ctx->epoch += 1;
+  ctx->epoch_rel[0] += 1;
   ctx->ev_valid[EV_H2D0] = ctx->staged_pending;  // h2d_us only when this join's inputs were staged
   ctx->staged_pending = false;
   ctx->h2d_pipelined = false;
@@ -730,7 +732,17 @@ extern "C" int rhj_histogram_rel(rhj_ctx *ctx, int which, const void *rel_dev, u
   RHJ_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = RHJ_OK;
-  if (which == 0) rc = begin_join(ctx, st);
+  if (which == 0) {
+    rc = begin_join(ctx, st);
+  } else {
+    // A further piece of the outer relation against the inner relation that is already partitioned
+    // (probe sides larger than the pool): everything outer-side starts over.
+    ctx->hist_done[1] = ctx->offsets_done[1] = ctx->rel_scattered[1] = ctx->rel_partitioned[1] = false;
+    ctx->wait_timed[1] = false;
+    ctx->local_planned = false;
+    ctx->stage = std::min(ctx->stage, 1);
+    ctx->epoch_rel[1] += 1;
+  }
   if (!rc) rc = set_input(ctx, which, rel_dev, n);
   if (!rc) rc = ctx->cfg.tuple_bytes == 16 ? histogram_chunks<16>(ctx, which, 0, ctx->nchunks1[which], st)
                                            : histogram_chunks<8>(ctx, which, 0, ctx->nchunks1[which], st);
@@ -883,7 +895,7 @@ extern "C" int rhj_network_partition_rel(rhj_ctx *ctx, int which, void *stream) 
     cudaStream_t sig = ctx->staged_exchange ? ctx->side : st;
     FlagPeers fp{};
     for (int r = 0; r < ctx->nranks; ++r) fp.addr[r] = ctx->peer_flags[r];
-    k_signal_peers<<<1, 64, 0, sig>>>(fp, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)k, ctx->epoch);
+    k_signal_peers<<<1, 64, 0, sig>>>(fp, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)k, ctx->epoch_rel[k]);
     RHJ_CHECK_LAUNCH("k_signal_peers");
   }
   if (ctx->staged_exchange) RHJ_CUDA(cudaEventRecord(ctx->ev_pushed[k], ctx->side));
@@ -966,7 +978,7 @@ extern "C" int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream) {
   ctx->wait_timed[which] = true;
   if (ctx->use_flags) {
     // every peer's stores of this relation have landed once its flag shows this join's epoch
-    k_wait_peers<<<1, 64, 0, st>>>(ctx->d_flags, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)which, ctx->epoch,
+    k_wait_peers<<<1, 64, 0, st>>>(ctx->d_flags, (uint32_t)ctx->nranks, (uint32_t)ctx->rank, (uint32_t)which, ctx->epoch_rel[which],
                                    5000000000ull, ctx->d_status);
     RHJ_CHECK_LAUNCH("k_wait_peers");
   }
@@ -1088,7 +1100,8 @@ static int launch_build_probe_cap(rhj_ctx *ctx, const BuildProbeArgs &a, cudaStr
   }
 }
 
-static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, bool emit, void *stream) {
+static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, bool emit, void *stream,
+                            bool keep_result = false) {
   if (!ctx) return fail(RHJ_ERR_INVALID, "ctx is NULL");
   if (!ctx->planned || ctx->stage < 4) return fail(RHJ_ERR_STATE, "rhj_local_partition first");
   if (emit && pairs_cap > 0 && !pairs_dev) return fail(RHJ_ERR_INVALID, "pairs_dev is NULL");
@@ -1100,7 +1113,7 @@ static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, b
     if (rc) return rc;
   }
   // the stage may be repeated on the same partitions (count first, then materialise)
-  RHJ_CUDA(cudaMemsetAsync(ctx->d_result, 0, 5 * 8, st));
+  if (!keep_result) RHJ_CUDA(cudaMemsetAsync(ctx->d_result, 0, 5 * 8, st));
   RHJ_CUDA(cudaMemsetAsync(ctx->d_work, 0, 2 * 8, st));
   if (ctx->nowned > 0) {
     BuildProbeArgs a{};
@@ -1135,6 +1148,10 @@ static int build_probe_impl(rhj_ctx *ctx, void *pairs_dev, uint64_t pairs_cap, b
 }
 
 extern "C" int rhj_build_probe(rhj_ctx *ctx, void *stream) { return build_probe_impl(ctx, nullptr, 0, false, stream); }
+
+extern "C" int rhj_build_probe_accumulate(rhj_ctx *ctx, void *stream) {
+  return build_probe_impl(ctx, nullptr, 0, false, stream, true);
+}
 
 extern "C" int rhj_build_probe_pairs(rhj_ctx *ctx, rhj_pair *pairs_dev, uint64_t capacity, void *stream) {
   return build_probe_impl(ctx, pairs_dev, capacity, true, stream);

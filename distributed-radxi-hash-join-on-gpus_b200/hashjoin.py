@@ -321,6 +321,74 @@ def join_multi_rank(ctx, inner: Relation, outer: Relation, group=None, pairs=Non
         ctx.build_probe()
 
 
+def host_pieces(outer_host, piece_tuples: int, device):
+    """Generator over device-resident pieces of a host relation (numpy array of 16-byte tuples or of packed
+    u64 values): two staging tensors and a copy stream, so that piece i+1 crosses PCIe while piece i is
+    joined.  A staging tensor is reused two pieces later, after the join stream has passed that point."""
+    import numpy as np
+    import torch
+    words = 2 if outer_host.dtype.itemsize == 16 else 1
+    flat = torch.from_numpy(np.ascontiguousarray(outer_host).view(np.int64))
+    n = len(outer_host)
+    bufs = [torch.empty(piece_tuples * words, dtype=torch.int64, device=device) for _ in range(2)]
+    free = [torch.cuda.Event() for _ in range(2)]
+    main, copy = torch.cuda.current_stream(), torch.cuda.Stream(device=device)
+    for i, b in enumerate(range(0, n, piece_tuples)):
+        m = min(piece_tuples, n - b)
+        buf = bufs[i & 1]
+        if i >= 2:
+            copy.wait_event(free[i & 1])  # the join of piece i-2 no longer reads this buffer
+        with torch.cuda.stream(copy):
+            buf[:m * words].copy_(flat[b * words:(b + m) * words], non_blocking=True)
+            arrived = torch.cuda.Event()
+            arrived.record(copy)
+        main.wait_event(arrived)
+        yield buf, m
+        free[i & 1].record(main)
+
+
+def join_probe_pieces(ctx, inner: Relation, pieces, group=None):
+    """HashJoin::join() with the probe side supplied piece by piece (SURVEY.md 8(f4)): the inner relation is
+    partitioned once and stays resident, every piece of the outer relation (device tensor, tuples) goes
+    through histogram, network pass, local pass and build/probe against it, and the results add up.  Only
+    the inner relation and one piece have to fit the context's plan.  Collective with more than one rank
+    (every rank supplies the same number of pieces).  Returns the rank's result of the whole join."""
+    import torch
+    import torch.distributed as dist
+    dev = f"cuda:{ctx.device}"
+    use_barrier = ctx.nranks > 1 and not ctx.has_flags()
+    token = torch.zeros(1, dtype=torch.int32, device=dev) if use_barrier else None
+
+    def phase(which, data, n):
+        ctx.histogram_rel(which, data, n)
+        if ctx.nranks > 1:
+            local = torch.as_tensor(_DeviceArray(ctx.local_histogram_ptr() + which * ctx.P * 8, ctx.P), device=dev)
+            gathered = torch.empty(ctx.nranks * ctx.P, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(gathered, local, group=group)
+            ctx.compute_offsets_rel(which, gathered)
+        else:
+            ctx.compute_offsets_rel(which, None)
+        ctx.network_partition_rel(which)
+        ctx.exchange_wait(which)
+        if use_barrier:
+            dist.all_reduce(token, group=group)
+        ctx.local_partition_rel(which)
+
+    phase(0, inner.data, inner.local_size)
+    first = True
+    for data, n in pieces:
+        phase(1, data, n)
+        if first:
+            ctx.build_probe()
+        else:
+            ctx.build_probe_accumulate()
+        first = False
+    if first:  # no pieces at all: an empty outer relation
+        phase(1, None, 0)
+        ctx.build_probe()
+    return ctx.result()
+
+
 class HashJoin:
     """hpcjoin::operators::HashJoin (operators/HashJoin.h:23-43).  RESULT_COUNTER is the
     class-level match count of the last join on this rank, as in the reference

@@ -242,6 +242,15 @@ int rhj_get_partition_dev(rhj_ctx *ctx, int which, uint32_t p, int after_local_p
 
 /* TASK_BUILD_PROBE -- tasks/BuildProbe.cpp:47-121 for every (sub-)partition pair this rank owns. */
 int rhj_build_probe(rhj_ctx *ctx, void *stream);
+/* The same, adding to the result of the build/probe calls before it instead of starting from zero: for a
+ * probe side that is joined piece by piece against an inner relation partitioned once (SURVEY.md 8(f4);
+ * the un-built kernel library planned this, data/data.hpp:17-20 MAX_CHUNK_SIZE, :83 iterCount).  Sequence:
+ * the inner relation's rhj_histogram_rel(0) .. rhj_local_partition_rel(0) once, then per outer piece
+ * rhj_histogram_rel(1, piece) -> rhj_compute_offsets_rel(1) -> rhj_network_partition_rel(1) ->
+ * rhj_exchange_wait(1) -> rhj_local_partition_rel(1) -> rhj_build_probe (first piece) or
+ * rhj_build_probe_accumulate (later pieces); rhj_get_result then holds the whole join.  Only the inner
+ * relation and ONE outer piece have to fit the planned maxima and windows. */
+int rhj_build_probe_accumulate(rhj_ctx *ctx, void *stream);
 /* The same stage with its output materialised: where the reference's probe loop
  * does `++matches` (tasks/BuildProbe.cpp:101-104; the unbuilt GPU probe kernels write pairs,
  * operators/gpu/kernels.cu:237-241), every match also appends one rhj_pair to `pairs_dev`

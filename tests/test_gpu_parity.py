@@ -163,6 +163,35 @@ def test_join_host_pipeline_many_pieces(rhj, oracle, monkeypatch):
     pin_o.free()
 
 
+@pytest.mark.parametrize("two_level", [True, False])
+def test_probe_side_in_pieces_larger_than_the_plan(rhj, oracle, two_level):
+    """an outer relation several times larger than the planned maximum and the receive
+    window, streamed from host memory in pieces against an inner relation that is partitioned once; count and
+    all four sums equal the oracle's join of the whole relations (the join is additive over the probe side)."""
+    import torch
+    cfg = rhj.make_config(5, 4, 27, two_level, chunk_tuples=8192)
+    inner = oracle.fill_perm(40000, 0, 40000, seed=5)
+    outer = oracle.fill_zipf(500003, 0, 40000, 1.0, seed=6)
+    want = oracle.join([inner], [outer], ocfg(oracle, cfg))[0].astuple()
+    piece = 65536
+    ctx = rhj.Context(cfg)
+    ctx.plan(len(inner), piece)                       # windows and maxima for ONE piece of the outer relation
+    with pytest.raises(rhj.RhjError):                 # the whole outer relation does not fit this plan
+        ctx.histogram(torch.zeros(2, dtype=torch.int64, device="cuda"), 1,
+                      torch.zeros(2, dtype=torch.int64, device="cuda"), len(outer))
+    di = torch.from_numpy(inner.view(np.int64).copy()).cuda()
+    rel = rhj.Relation(di, len(inner), len(inner))
+    for _ in range(2):                                # twice: every piece restarts the outer-side state
+        got = rhj.join_probe_pieces(ctx, rel, rhj.host_pieces(outer, piece, "cuda:0"))
+        assert got.astuple() == want
+    # an empty outer relation, and pieces that are already on the device
+    assert rhj.join_probe_pieces(ctx, rel, iter(())).matches == 0
+    do = torch.from_numpy(outer.view(np.int64).copy()).cuda()
+    dev_pieces = ((do[2 * b:], min(piece, len(outer) - b)) for b in range(0, len(outer), piece))
+    assert rhj.join_probe_pieces(ctx, rel, dev_pieces).astuple() == want
+    ctx.close()
+
+
 def test_window_overflow_is_reported(rhj, oracle):
     inner, outer = oracle.generate_reference(1, 50000, 50000)
     run = GpuRun(rhj, rhj.make_config(4, 4, 28, True), inner, outer, window_caps=(1000, 1000))
