@@ -234,3 +234,44 @@ def test_device_distribute_two_gpus(oracle, tmp_path):
     oracle.distribute_perm(rels, seed)
     for r in range(world):
         assert np.array_equal(np.load(tmp_path / f"dist{r}.npy"), rels[r].view(np.uint64).reshape(-1, 2))
+
+
+def _worker_pieces(rank, world, port, per_r, per_s, piece, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    inner, outer = O.generate_reference(world, per_r, per_s, gen="modulo")
+    cfg = rhj.make_config(6, 5, 26, True, chunk_tuples=8192)
+    ctx = rhj.Context(cfg, rank, world, rank)
+    ctx.plan(per_r, piece, per_r * world, piece * world)  # windows for one piece per rank, whatever its keys
+    rhj.hashjoin.exchange_windows(ctx)
+    rel = rhj.Relation.from_numpy(inner[rank], per_r * world, device=rank)
+    res = [rhj.join_probe_pieces(ctx, rel, rhj.host_pieces(outer[rank], piece, f"cuda:{rank}")).astuple()
+           for _ in range(2)]
+    np.save(os.path.join(out_dir, f"pieces{rank}.npy"), np.array(res, dtype=np.uint64))
+    dist.barrier()
+    ctx.close()
+    dist.destroy_process_group()
+
+
+def test_probe_side_in_pieces_two_gpus(oracle, tmp_path):
+    """SURVEY.md 8(f4) on two ranks: every rank streams its share of an outer relation eight times the inner
+    one from host memory in pieces; each rank's result equals the oracle's for the whole relations."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    world, per_r, per_s, piece = 2, 30000, 240000, 32768
+    mp.spawn(_worker_pieces, args=(world, _free_port(), per_r, per_s, piece, str(tmp_path)), nprocs=world, join=True)
+    inner, outer = oracle.generate_reference(world, per_r, per_s, gen="modulo")
+    want = oracle.join(inner, outer, oracle.Config(6, 5, 26, 1))
+    for r in range(world):
+        got = np.load(tmp_path / f"pieces{r}.npy")
+        for rep in range(2):
+            assert tuple(int(x) for x in got[rep]) == want[r].astuple()
