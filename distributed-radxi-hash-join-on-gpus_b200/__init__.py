@@ -416,4 +416,4 @@ def apply_perm(tensor, n: int, stride_words: int, domain: int, seed: int):
     check(lib().rhj_apply_perm(_ptr(tensor), n, stride_words, domain, seed, _stream()))
 
 
-from .hashjoin import HashJoin, Relation, distribute, host_pieces, join_multi_rank, join_probe_pieces  # noqa: E402,F401
+from .hashjoin import HashJoin, HotSplitJoin, Relation, distribute, host_pieces, join_multi_rank, join_probe_pieces  # noqa: E402,F401

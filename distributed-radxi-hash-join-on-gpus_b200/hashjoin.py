@@ -389,6 +389,109 @@ def join_probe_pieces(ctx, inner: Relation, pieces, group=None):
     return ctx.result()
 
 
+def hot_partitions(global_outer, nranks: int, inv_share: int = 4):
+    """The skew rule, identical on every rank (second half), in integer arithmetic: a network
+    partition is HOT when its probe-side tuple count exceeds 1/inv_share of the mean probe-side load of a rank,
+    i.e. global_outer[p] * nranks * inv_share > sum(global_outer) -- a single partition that alone is a quarter
+    (by default) of what a rank should carry.  Uniform keys never trigger it (a partition is 1/P of the
+    relation, and P >= 4 n in every configuration this repo runs).  inv_share <= 0 switches splitting off.
+    `global_outer`: int64[P] (torch tensor or numpy array).  Returns a boolean mask over partitions."""
+    if inv_share <= 0:
+        return global_outer < 0
+    return global_outer * (nranks * inv_share) > global_outer.sum()
+
+
+def split_hot(rel: Relation, hot_mask, P: int):
+    """(hot part, cold part) of a relation of 16-byte tuples as two new int64 tensors [m, 2]."""
+    t = rel.data[:2 * rel.local_size].view(-1, 2)
+    is_hot = hot_mask[t[:, 0] & (P - 1)]
+    return t[is_hot].contiguous(), t[~is_hot].contiguous()
+
+
+def gather_rows(local_rows, nranks: int, group=None):
+    """All ranks' rows ([m_r, 2] int64, m_r differs per rank) concatenated in rank order on every rank."""
+    import torch
+    import torch.distributed as dist
+    if nranks == 1:
+        return local_rows
+    cnt = torch.tensor([local_rows.shape[0]], dtype=torch.int64, device=local_rows.device)
+    cnts = [torch.zeros_like(cnt) for _ in range(nranks)]
+    dist.all_gather(cnts, cnt, group=group)
+    sizes = [int(c.item()) for c in cnts]
+    pad = max(max(sizes), 1)
+    mine = torch.zeros((pad, 2), dtype=torch.int64, device=local_rows.device)
+    mine[:local_rows.shape[0]] = local_rows
+    bufs = [torch.empty_like(mine) for _ in range(nranks)]
+    dist.all_gather(bufs, mine, group=group)
+    return torch.cat([b[:m] for b, m in zip(bufs, sizes)])
+
+
+class HotSplitJoin:
+    """HashJoin with hot-partition splitting (the part a partition -> rank assignment cannot
+    do): the probe side of a hot partition is NOT sent to the partition's owner -- every rank keeps its own
+    tuples of it -- and the partition's build side is replicated to all ranks instead, so a hot key's matches
+    are spread like the probe tuples themselves.  What the reference's un-built kernels do inside one GPU
+    (skew_detect / generate_block_mapping / probe_skew, operators/gpu/kernels_optimized.cu:301-364), done across
+    ranks.  Built from the library's own stages: the cold partitions go through the ordinary multi-rank join,
+    the hot ones through a second, single-rank context per GPU (inner = the replicated build side, outer =
+    this rank's probe tuples); the two results add up.  Splitting and replication are launcher plumbing
+    (torch indexing, one all-gather of the hot build tuples); `hot_partitions` is the rule.
+    16-byte tuples; every rank constructs and calls it alike."""
+
+    def __init__(self, numberOfNodes: int, nodeId: int, innerRelation: Relation, outerRelation: Relation,
+                 config=None, device=None, group=None, inv_share: int = 4):
+        import copy
+        import torch
+        import torch.distributed as dist
+        from . import Context, make_config
+        self.n, self.rank, self.group, self.inv_share = numberOfNodes, nodeId, group, inv_share
+        self.inner, self.outer = innerRelation, outerRelation
+        cfg = config if config is not None else make_config()
+        self.cfg = cfg
+        self.P = 1 << cfg.network_fanout_bits
+        dev = device if device is not None else torch.cuda.current_device()
+        self.device = dev
+        # the rule needs the global probe-side histogram: one counting pass at construction, as for the windows
+        keys = outerRelation.data[:2 * outerRelation.local_size:2]
+        h = torch.bincount(keys & (self.P - 1), minlength=self.P)
+        if numberOfNodes > 1:
+            dist.all_reduce(h, group=group)
+        self.hot = hot_partitions(h, numberOfNodes, inv_share)
+        s_hot, s_cold = split_hot(outerRelation, self.hot, self.P)
+        r_hot, r_cold = split_hot(innerRelation, self.hot, self.P)
+        self.r_hot_all = gather_rows(r_hot, numberOfNodes, group)
+        self.s_hot = s_hot
+        self.cold_inner = Relation(r_cold.view(-1), r_cold.shape[0], innerRelation.global_size)
+        self.cold_outer = Relation(s_cold.view(-1), s_cold.shape[0], outerRelation.global_size)
+        # ragged cold sizes per rank: plan the main context for the largest share
+        sizes = torch.tensor([r_cold.shape[0], s_cold.shape[0]], dtype=torch.int64, device=r_cold.device)
+        if numberOfNodes > 1:
+            dist.all_reduce(sizes, op=dist.ReduceOp.MAX, group=group)
+        self.ctx = Context(cfg, nodeId, numberOfNodes, dev)
+        caps = (0, 0) if numberOfNodes == 1 else exact_window_caps(cfg, numberOfNodes, nodeId, self.cold_inner,
+                                                                    self.cold_outer, group)
+        self.ctx.plan(max(int(sizes[0].item()), 1), max(int(sizes[1].item()), 1), *caps)
+        exchange_windows(self.ctx, group)
+        hot_cfg = copy.copy(cfg)
+        self.hot_ctx = Context(hot_cfg, 0, 1, dev)
+        self.hot_ctx.plan(max(self.r_hot_all.shape[0], 1), max(s_hot.shape[0], 1))
+
+    def join(self):
+        from . import Result
+        join_multi_rank(self.ctx, self.cold_inner, self.cold_outer, self.group)
+        cold = self.ctx.result()
+        hot = self.hot_ctx.join(self.r_hot_all.view(-1), self.r_hot_all.shape[0], self.s_hot.view(-1), self.s_hot.shape[0])
+        m = (1 << 64) - 1
+        out = Result(*[(a + b) & m for a, b in zip(cold.astuple(), hot.astuple())])
+        HashJoin.RESULT_COUNTER = out.matches
+        HashJoin.RESULT_CHECKSUM = out.astuple()[1:]
+        return out
+
+    def close(self):
+        self.ctx.close()
+        self.hot_ctx.close()
+
+
 class HashJoin:
     """hpcjoin::operators::HashJoin (operators/HashJoin.h:23-43).  RESULT_COUNTER is the
     class-level match count of the last join on this rank, as in the reference

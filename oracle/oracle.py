@@ -294,6 +294,32 @@ def join_pairs(inner: list, outer: list, cfg: Config, cap: int) -> tuple:
     return list(res), [bufs[r][: min(sinks[r].n, cap)] for r in range(nranks)]
 
 
+def join_hot_split(inner: list, outer: list, cfg: Config, inv_share: int = 4) -> tuple:
+    """Per-rank results under hot-partition splitting, stated independently of the launcher: a partition p is
+    hot when global_outer[p] * nranks * inv_share > sum(global_outer); the cold partitions are joined as
+    orc_join does, and rank r additionally joins ALL ranks' inner tuples of the hot partitions with ITS OWN
+    outer tuples of them.  Returns (results per rank, hot mask)."""
+    n = len(inner)
+    P = 1 << cfg.net_bits
+    glob = np.zeros(P, np.uint64)
+    for t in outer:
+        glob += local_histogram(t, cfg)
+    hot = (glob.astype(object) * (n * inv_share) > int(glob.sum())) if inv_share > 0 else np.zeros(P, bool)
+    hot = np.array(hot, dtype=bool)
+    pid = lambda t: (t["key"] & np.uint64(P - 1)).astype(np.int64)
+    cold_i = [np.ascontiguousarray(t[~hot[pid(t)]]) for t in inner]
+    cold_o = [np.ascontiguousarray(t[~hot[pid(t)]]) for t in outer]
+    res = join(cold_i, cold_o, cfg)
+    hot_r = np.ascontiguousarray(np.concatenate([t[hot[pid(t)]] for t in inner]))
+    m = (1 << 64) - 1
+    out = []
+    for r in range(n):
+        hot_s = np.ascontiguousarray(outer[r][hot[pid(outer[r])]])
+        h = join([hot_r], [hot_s], cfg)[0]
+        out.append(tuple((a + b) & m for a, b in zip(res[r].astuple(), h.astuple())))
+    return out, hot
+
+
 def total(results) -> tuple:
     m = (1 << 64) - 1
     acc = [0, 0, 0, 0, 0]

@@ -275,3 +275,52 @@ def test_probe_side_in_pieces_two_gpus(oracle, tmp_path):
         got = np.load(tmp_path / f"pieces{r}.npy")
         for rep in range(2):
             assert tuple(int(x) for x in got[rep]) == want[r].astuple()
+
+
+def _worker_hot_split(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    inner = O.fill_perm(60000, rank * 60000, 60000 * world, seed=9)
+    outer = O.fill_zipf(300000, rank * 300000, 60000 * world, 1.0, seed=20 + rank)
+    cfg = rhj.make_config(6, 4, 26, True)
+    ri = rhj.Relation.from_numpy(inner, 60000 * world, device=rank)
+    ro = rhj.Relation.from_numpy(outer, 300000 * world, device=rank)
+    hj = rhj.HotSplitJoin(world, rank, ri, ro, config=cfg, device=rank, inv_share=16)
+    res = [hj.join().astuple() for _ in range(2)]
+    plain = rhj.HashJoin(world, rank, ri, ro, config=cfg, device=rank)
+    res.append(plain.join().astuple())
+    np.save(os.path.join(out_dir, f"hot{rank}.npy"), np.array(res, dtype=np.uint64))
+    dist.barrier()
+    hj.close()
+    plain.close()
+    dist.destroy_process_group()
+
+
+def test_hot_partition_splitting_two_gpus(oracle, tmp_path):
+    """SURVEY.md 8(f3), second half: per-rank results under hot-partition splitting equal the oracle-side
+    statement of the rule; the sum equals the plain join's; the busiest rank's matches drop."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    world = 2
+    mp.spawn(_worker_hot_split, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    inner = [oracle.fill_perm(60000, r * 60000, 60000 * world, seed=9) for r in range(world)]
+    outer = [oracle.fill_zipf(300000, r * 300000, 60000 * world, 1.0, seed=20 + r) for r in range(world)]
+    cfg = oracle.Config(6, 4, 26, 1)
+    want, hot = oracle.join_hot_split(inner, outer, cfg, 16)
+    assert hot.any() and not hot.all()
+    plain = oracle.join(inner, outer, cfg)
+    got = [np.load(tmp_path / f"hot{r}.npy") for r in range(world)]
+    for r in range(world):
+        for rep in range(2):
+            assert tuple(int(x) for x in got[r][rep]) == want[r]
+        assert tuple(int(x) for x in got[r][2]) == plain[r].astuple()
+    assert max(w[0] for w in want) < max(p.matches for p in plain)

@@ -192,6 +192,23 @@ def test_probe_side_in_pieces_larger_than_the_plan(rhj, oracle, two_level):
     ctx.close()
 
 
+def test_hot_split_join_single_rank(rhj, oracle):
+    """HotSplitJoin on one rank: the hot partitions go through the second context, the rest through the first;
+    the sum equals the plain join (and the oracle's statement of the rule, which on one rank is the same)."""
+    import torch
+    inner = oracle.fill_perm(50000, 0, 50000, seed=9)
+    outer = oracle.fill_zipf(200000, 0, 50000, 1.0, seed=21)
+    cfg = rhj.make_config(6, 4, 26, True)
+    ri = rhj.Relation.from_numpy(inner, 50000)
+    ro = rhj.Relation.from_numpy(outer, 200000)
+    hj = rhj.HotSplitJoin(1, 0, ri, ro, config=cfg, device=0, inv_share=32)
+    assert bool(hj.hot.any()) and hj.s_hot.shape[0] > 0
+    want, hot = oracle.join_hot_split([inner], [outer], ocfg(oracle, cfg), 32)
+    assert np.array_equal(hj.hot.cpu().numpy(), hot)
+    assert hj.join().astuple() == want[0] == oracle.join([inner], [outer], ocfg(oracle, cfg))[0].astuple()
+    hj.close()
+
+
 def test_window_overflow_is_reported(rhj, oracle):
     inner, outer = oracle.generate_reference(1, 50000, 50000)
     run = GpuRun(rhj, rhj.make_config(4, 4, 28, True), inner, outer, window_caps=(1000, 1000))

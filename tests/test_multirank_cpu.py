@@ -130,3 +130,51 @@ def test_perm_positions_equals_oracle(oracle):
         want = np.array([oracle.lib().orc_perm(i, n, seed) for i in range(n)], np.int64)
         assert np.array_equal(got, want), (n, seed)
         assert np.array_equal(np.sort(got), np.arange(n))
+
+
+def _worker_hot(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    H = rhj.hashjoin
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    P = 64
+    inner = O.fill_perm(6000, rank * 6000, 6000 * world, seed=9)
+    outer = O.fill_zipf(20000, rank * 20000, 6000 * world, 1.0, seed=10 + rank)
+    ri = rhj.Relation(torch.from_numpy(inner.view(np.int64).copy()), len(inner), 6000 * world)
+    ro = rhj.Relation(torch.from_numpy(outer.view(np.int64).copy()), len(outer), 20000 * world)
+    h = torch.bincount(ro.data[::2] & (P - 1), minlength=P)
+    dist.all_reduce(h)
+    hot = H.hot_partitions(h, world, 8)
+    s_hot, s_cold = H.split_hot(ro, hot, P)
+    r_hot, r_cold = H.split_hot(ri, hot, P)
+    r_all = H.gather_rows(r_hot, world)
+    np.savez(os.path.join(out_dir, f"hot{rank}.npz"), hot=hot.numpy(), s_hot=s_hot.numpy(), s_cold=s_cold.numpy(),
+             r_cold=r_cold.numpy(), r_all=r_all.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_hot_partition_rule_and_split_plumbing(oracle, tmp_path):
+    """hot_partitions / split_hot / gather_rows (launcher plumbing of HotSplitJoin) over gloo against the
+    oracle-side statement of the rule (oracle.join_hot_split)."""
+    import torch.multiprocessing as mp
+    world, P = 3, 64
+    mp.spawn(_worker_hot, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    inner = [oracle.fill_perm(6000, r * 6000, 6000 * world, seed=9) for r in range(world)]
+    outer = [oracle.fill_zipf(20000, r * 20000, 6000 * world, 1.0, seed=10 + r) for r in range(world)]
+    _, hot = oracle.join_hot_split(inner, outer, oracle.Config(6, 3, 26, 1), 8)
+    assert hot.any() and not hot.all()
+    pid = lambda t: (t["key"] & np.uint64(P - 1)).astype(np.int64)
+    want_r_all = np.concatenate([t[hot[pid(t)]] for t in inner]).view(np.int64).reshape(-1, 2)
+    for r in range(world):
+        z = np.load(tmp_path / f"hot{r}.npz")
+        assert np.array_equal(z["hot"], hot)
+        assert np.array_equal(z["r_all"], want_r_all)
+        assert np.array_equal(z["s_hot"], outer[r][hot[pid(outer[r])]].view(np.int64).reshape(-1, 2))
+        assert np.array_equal(z["s_cold"], outer[r][~hot[pid(outer[r])]].view(np.int64).reshape(-1, 2))
+        assert np.array_equal(z["r_cold"], inner[r][~hot[pid(inner[r])]].view(np.int64).reshape(-1, 2))

@@ -126,3 +126,19 @@ def test_balanced_assignment_moves_partitions_not_results(oracle, nranks):
     assert oracle.total(bal) == oracle.bruteforce(np.concatenate(inner), np.concatenate(outer)).astuple()
     assert max(r.matches for r in bal) <= max(r.matches for r in rr)
     assert [r.matches for r in bal] != [r.matches for r in rr]
+
+
+def test_hot_split_total_equals_plain_join_and_balances(oracle):
+    """oracle.join_hot_split: the split changes who counts a match, never the sum; the busiest rank's share drops."""
+    world = 4
+    cfg = oracle.Config(6, 3, 26, 1)
+    inner = [oracle.fill_perm(6000, r * 6000, 6000 * world, seed=9) for r in range(world)]
+    outer = [oracle.fill_zipf(30000, r * 30000, 6000 * world, 1.0, seed=20 + r) for r in range(world)]
+    plain = oracle.join(inner, outer, cfg)
+    split, hot = oracle.join_hot_split(inner, outer, cfg, 8)
+    assert hot.any() and not hot.all()
+    m = (1 << 64) - 1
+    assert tuple(sum(s[i] for s in split) & m for i in range(5)) == oracle.total(plain)
+    assert max(s[0] for s in split) < max(p.matches for p in plain)
+    none, hot0 = oracle.join_hot_split(inner, outer, cfg, 0)
+    assert not hot0.any() and [tuple(x) for x in none] == [p.astuple() for p in plain]
