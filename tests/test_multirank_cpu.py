@@ -178,3 +178,45 @@ def test_hot_partition_rule_and_split_plumbing(oracle, tmp_path):
         assert np.array_equal(z["s_hot"], outer[r][hot[pid(outer[r])]].view(np.int64).reshape(-1, 2))
         assert np.array_equal(z["s_cold"], outer[r][~hot[pid(outer[r])]].view(np.int64).reshape(-1, 2))
         assert np.array_equal(z["r_cold"], inner[r][~hot[pid(inner[r])]].view(np.int64).reshape(-1, 2))
+
+
+def _worker_caps(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    rhj = importlib.import_module("distributed-radxi-hash-join-on-gpus_b200")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    inner = O.fill_perm(5000 + 100 * rank, rank * 6000, 6000 * world, seed=9)
+    outer = O.fill_zipf(20000, rank * 20000, 6000 * world, 1.0, seed=10 + rank)
+    out = {}
+    for name, flags in (("plain", 0), ("balanced", rhj.FLAG_BALANCED_ASSIGNMENT)):
+        cfg = rhj.make_config(5, 4, 27, True, flags=flags)
+        ri = rhj.Relation(torch.from_numpy(inner.view(np.int64).copy()), len(inner), 6000 * world)
+        ro = rhj.Relation(torch.from_numpy(outer.view(np.int64).copy()), len(outer), 20000 * world)
+        out[name] = np.array(rhj.hashjoin.exact_window_caps(cfg, world, rank, ri, ro), np.uint64)
+    np.savez(os.path.join(out_dir, f"caps{rank}.npz"), **out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_exact_window_caps_equal_the_reference_window_sizes(oracle, tmp_path):
+    """The launchers size the receive windows as the reference does (data/Window.cpp:160-178): from the
+    histograms.  exact_window_caps over gloo against the oracle's plan, p % n and size-balanced assignment."""
+    import torch.multiprocessing as mp
+    world = 3
+    mp.spawn(_worker_caps, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    inner = [oracle.fill_perm(5000 + 100 * r, r * 6000, 6000 * world, seed=9) for r in range(world)]
+    outer = [oracle.fill_zipf(20000, r * 20000, 6000 * world, 1.0, seed=10 + r) for r in range(world)]
+    cfg = oracle.Config(5, 4, 27, 1)
+    li = np.stack([oracle.local_histogram(t, cfg) for t in inner])
+    lo = np.stack([oracle.local_histogram(t, cfg) for t in outer])
+    bal = oracle.balanced_assignment(li.sum(axis=0, dtype=np.uint64), lo.sum(axis=0, dtype=np.uint64), world)
+    for name, assign in (("plain", None), ("balanced", bal)):
+        want = (int(oracle.plan(li, world, assign).window_size.max()) + 64,
+                int(oracle.plan(lo, world, assign).window_size.max()) + 64)
+        for r in range(world):
+            got = np.load(tmp_path / f"caps{r}.npz")[name]
+            assert (int(got[0]), int(got[1])) == want, (name, r)
