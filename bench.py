@@ -435,9 +435,24 @@ def run_ours(args):
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         check(r)
+        # what the host can deliver at all: the same pinned buffers copied to the device and nothing else,
+        # all ranks at once (the e2e step cannot be faster than this)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(2):
+            rhj.check(L.rhj_memcpy_h2d(d_inner.data_ptr(), pin_i.ptr, nbytes))
+            rhj.check(L.rhj_memcpy_h2d(d_outer.data_ptr(), pin_o.ptr, nbytes))
+        barrier()
+        dc = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dc, op=dist.ReduceOp.MAX)
+        h2d_only_ms = float(dc.item()) * 1e3 / 2
         e2e = {"value": 2.0 * G * args.e2e_steps / float(dt.item()), "unit": UNIT,
                "h2d_bytes_per_step": 2 * nbytes * world, "d2h_bytes_per_step": 40 * world,
                "steps": args.e2e_steps, "ms_per_step": float(dt.item()) * 1e3 / args.e2e_steps,
+               "h2d_only_ms_per_step": h2d_only_ms,
+               "h2d_only_GBps_per_gpu": 2 * nbytes / (h2d_only_ms * 1e-3) / 1e9,
+               "step_over_h2d_only": float(dt.item()) * 1e3 / args.e2e_steps / h2d_only_ms,
                "api": "rhj_join_host (pinned host buffers)" if world == 1 else
                       "rhj_stage_host_inputs (pinned host buffers) + the stage entry points, one process per GPU"}
     clocks = sampler.stop() if rank == 0 else None

@@ -267,6 +267,11 @@ void Measurements::storeAllMeasurements() {
   fprintf(f, "JPROC\t%lu\tus\n", (unsigned long)last.jproc_us);
   fprintf(f, "LPTASKTIME\t%lu\tus\n", (unsigned long)last.lp_us);
   fprintf(f, "BPTASKTIME\t%lu\tus\n", (unsigned long)last.bp_us);
+  // special keys (performance/Measurements.cpp:176-178): the windows are carved when the context is planned and
+  // the local pass needs no preparation step here, so only the wait for the network phase is non-zero
+  fprintf(f, "SWINALLOC\t%lu\tus\n", 0ul);
+  fprintf(f, "SNETCOMPL\t%lu\tus\n", (unsigned long)last.snetcompl_us);
+  fprintf(f, "SLOCPREP\t%lu\tus\n", 0ul);
   fprintf(f, "JWALL\t%lu\tus\n", (unsigned long)wallJoinUs);
   fclose(f);
 }
@@ -280,6 +285,13 @@ void Measurements::printMeasurements(uint32_t numberOfNodes, uint32_t, const std
   printf("\n[RESULTS] Join:\t%.3f\n", last.jtotal_us / 1000.0);
   printf("[RESULTS] Summary:\t%lu\t%.3f\t%.3f\t%.3f\t%.3f\n", (unsigned long)total, last.jtotal_us / 1000.0,
          last.jhist_us / 1000.0, last.jmpi_us / 1000.0, last.jproc_us / 1000.0);
+}
+// the ten values a rank sends to the aggregator (performance/Measurements.cpp:548-565, serializeResults):
+// matches, total, histogram, network, local phase, window allocation, network completion wait, local
+// preparation, local-partitioning task sum, build/probe task sum (times in microseconds)
+std::vector<uint64_t> Measurements::serializeResults(uint64_t matches) {
+  return {matches, (uint64_t)last.jtotal_us, (uint64_t)last.jhist_us, (uint64_t)last.jmpi_us, (uint64_t)last.jproc_us,
+          0, (uint64_t)last.snetcompl_us, 0, (uint64_t)last.lp_us, (uint64_t)last.bp_us};
 }
 }  // namespace performance
 

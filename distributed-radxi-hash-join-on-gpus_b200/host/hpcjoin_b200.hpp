@@ -139,6 +139,7 @@ class Measurements {
   static void stopJoin(rhj_ctx *ctx);
   static void storeAllMeasurements();
   static void printMeasurements(uint32_t numberOfNodes, uint32_t nodeId, const std::vector<uint64_t> &tuplesPerNode);
+  static std::vector<uint64_t> serializeResults(uint64_t matches);  // performance/Measurements.cpp:548-565
   static rhj_timings last;
   static double wallJoinUs;
  private:

@@ -35,10 +35,19 @@ static int rank_main(data::ProcessComm &comm, void *argp) {
                       operators::HashJoin::RESULT_CHECKSUM[3]};
   std::vector<uint64_t> all(5 * numberOfNodes);
   comm.allgatherHost(mine, all.data(), sizeof(mine));
+  // the reference's per-rank 10-tuple (matches, total, hist, network, local, winalloc, netwait, locprep, LP sum, BP sum)
+  const std::vector<uint64_t> ten = performance::Measurements::serializeResults(operators::HashJoin::RESULT_COUNTER);
+  std::vector<uint64_t> tens(10 * numberOfNodes);
+  comm.allgatherHost(ten.data(), tens.data(), 10 * sizeof(uint64_t));
   if (nodeId == 0) {
     std::vector<uint64_t> counts(numberOfNodes);
     for (uint32_t r = 0; r < numberOfNodes; ++r) counts[r] = all[5 * r];
     performance::Measurements::printMeasurements(numberOfNodes, nodeId, counts);
+    for (uint32_t r = 0; r < numberOfNodes; ++r) {
+      printf("[RESULTS] Rank %u:", r);
+      for (int i = 0; i < 10; ++i) printf("\t%lu", (unsigned long)tens[10 * r + i]);
+      printf("\n");
+    }
     for (uint32_t r = 0; r < numberOfNodes; ++r)
       printf("[RESULTS] Checksum%s:\t%lu\t%lu\t%lu\t%lu\n", numberOfNodes > 1 ? (" rank " + std::to_string(r)).c_str() : "",
              (unsigned long)all[5 * r + 1], (unsigned long)all[5 * r + 2], (unsigned long)all[5 * r + 3],

@@ -35,6 +35,9 @@ def test_cpp_hashjoin_matches_oracle(rhj, oracle, knobs, tmp_path):
     assert p.returncode == 0, p.stderr
     tuples = int(re.search(r"\[RESULTS\] Tuples:\t(\d+)", p.stdout).group(1))
     chk = tuple(int(x) for x in re.search(r"\[RESULTS\] Checksum:\t(\d+)\t(\d+)\t(\d+)\t(\d+)", p.stdout).groups())
+    # the reference's per-rank 10-tuple (performance/Measurements.cpp:548-565): matches first, then times
+    ten = [int(x) for x in re.search(r"\[RESULTS\] Rank 0:((?:\t\d+){10})", p.stdout).group(1).split()]
+    assert ten[0] == tuples and ten[1] > 0 and ten[5] == 0 and ten[7] == 0
     inner, outer = oracle.generate_reference(1, n, n)
     want = oracle.join(inner, outer, oracle.Config(*knobs))[0].astuple()
     assert (tuples,) + chk == want
