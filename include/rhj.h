@@ -205,9 +205,11 @@ int rhj_get_base_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *stre
 int rhj_get_write_offsets(rhj_ctx *ctx, int which, uint64_t *out_host, void *stream);
 
 /* TASK_NET_PARTITION -- tasks/NetworkPartitioning.cpp:74-222 + data/Window.cpp:86-144:
- * radix scatter on the low key bits with 16->8 byte compression, written straight
- * into the owning rank's window (peer stores replace MPI_Put).  Uses the inputs
- * given to rhj_histogram.  All ranks must finish (barrier) before the next stage. */
+ * radix scatter on the low key bits with 16->8 byte compression through write-combining buffers
+ * (cacheline_t, :28-40): whole 128-byte lines go into the owning rank's window -- directly (one or two
+ * ranks: peer stores replace MPI_Put) or through a send buffer that is pushed as sequential runs (three and
+ * more ranks; RHJ_FLAG_STAGED_EXCHANGE / RHJ_FLAG_DIRECT_EXCHANGE).  Uses the inputs given to rhj_histogram.
+ * The local pass of a relation may start once every rank's stores of it have landed: rhj_exchange_wait. */
 int rhj_network_partition(rhj_ctx *ctx, void *stream);
 /* The same, one relation at a time (which: 0 inner, 1 outer), on a stream of the caller's choice, so that
  * a multi-rank launcher can start the inner relation's barrier + local pass while the outer relation is
@@ -222,11 +224,13 @@ int rhj_set_sm_limit(rhj_ctx *ctx, int sms);
 int rhj_local_partition(rhj_ctx *ctx, void *stream);
 /* The same, one relation at a time (which: 0 inner, 1 outer), so that a multi-rank launcher can
  * start the inner relation's local pass while the outer relation is still crossing NVLink:
- *   rhj_network_partition -> rhj_exchange_wait(0) -> barrier -> rhj_local_partition_rel(0)
- *                         -> rhj_exchange_wait(1) -> barrier -> rhj_local_partition_rel(1) -> rhj_build_probe
+ *   rhj_network_partition -> rhj_exchange_wait(0) -> [barrier] -> rhj_local_partition_rel(0)
+ *                         -> rhj_exchange_wait(1) -> [barrier] -> rhj_local_partition_rel(1) -> rhj_build_probe
  * rhj_exchange_wait makes `stream` wait until THIS rank's stores of relation `which` into its
- * peers' windows are complete (MPI_Win_flush_local_all, data/Window.cpp:193-201); the barrier
- * that follows (operators/HashJoin.cpp:119-121) then means every rank's are. */
+ * peers' windows are complete (MPI_Win_flush_local_all, data/Window.cpp:193-201) and -- when
+ * rhj_exchange_has_flags() -- until every peer's arrival flag for the relation is set, which is the barrier
+ * of operators/HashJoin.cpp:119-121; without flags the launcher's own barrier goes where [barrier] stands.
+ * The time between this call and the relation's local pass is reported as rhj_timings.snetcompl_us. */
 int rhj_exchange_wait(rhj_ctx *ctx, int which, void *stream);
 /* Host-blocking form of rhj_exchange_wait, for launchers whose barrier is a host-side one
  * (MPI_Barrier, gloo). */
